@@ -1,0 +1,182 @@
+/*
+ * pyrecover_b200.h -- C ABI of libpyrecover_b200.so (sm_100a only).
+ *
+ * The reference (Shaswat-G/PyRecover) is pure Python and has no FFI of its own; the three
+ * places where its training step hands work to native code are library calls made from
+ * train.py and pyrecover/checkpoint.py.  Each entry point below names the reference call
+ * site it stands in for.  The Python binding a maintainer adds is in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns 0 (PR_OK) or a negative pr_status; pr_last_error() gives the
+ *     text of the last failure on the calling thread.  No exception crosses the boundary.
+ *   - pointers named *_dev are device pointers, *_host are host pointers; `stream` is a
+ *     cudaStream_t passed as void* (NULL = the legacy default stream).
+ *   - the caller owns every buffer it passes; the library borrows it until the work queued
+ *     on `stream` has completed.
+ *   - there is no CPU fallback: without a Blackwell GPU the calls fail with PR_ERR_CUDA.
+ */
+#ifndef PYRECOVER_B200_H
+#define PYRECOVER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PR_ABI_VERSION 1
+#define PR_MAX_WORLD 8            /* one NVSwitch domain: 8 x B200                          */
+#define PR_MAX_REGIONS 4          /* symmetric regions per communicator                     */
+#define PR_EXPORT_BLOB_BYTES 512  /* bytes pr_comm_export writes per rank                   */
+
+typedef enum pr_status {
+    PR_OK = 0,
+    PR_ERR_INVALID = -1,   /* bad argument (null, misaligned, out of range)                 */
+    PR_ERR_CUDA = -2,      /* a CUDA runtime call failed; text in pr_last_error()           */
+    PR_ERR_UNSUPPORTED = -3,
+    PR_ERR_STATE = -4,     /* call made in the wrong state (e.g. allreduce before import)   */
+    PR_ERR_IO = -5
+} pr_status;
+
+typedef enum pr_dtype { PR_BF16 = 0, PR_F32 = 1 } pr_dtype;
+
+/* Last error text for this thread ("" if none).  Never NULL. */
+const char *pr_last_error(void);
+int pr_abi_version(void);
+/* SM count / compute capability of the current device. */
+int pr_device_info(int *sm_count, int *cc_major, int *cc_minor);
+
+/* ---------------------------------------------------------------- K2: AdamW ----------
+ * Replaces optimizer.step() -- reference train.py:274, constructed at train.py:120-122 as
+ * torch.optim.AdamW(model.parameters(), lr, fused=args.fused_optimizer); the arithmetic is
+ * torch/optim/adam.py:347-551 (_single_tensor_adam) / :803-900 (_fused_adamw_).
+ * One launch updates a flat arena of n elements: p, m, v in place, g read-only.
+ *   numerics = 0: fp32 op-math, one rounding at the store  (class of fused=True)
+ *   numerics = 1: result of every torch op rounded to the storage dtype (class of the
+ *                 reference's default fused=False path on bf16 tensors)
+ * lr is a runtime scalar because the reference's LambdaLR (utils.py:59-81, train.py:275)
+ * changes it every warm-up step.  `step` is the 1-based step count t of this update.
+ * grad_scale multiplies g first (1/W of the DDP mean, or a loss-scale inverse); 1.0 = off.
+ * grad_dtype may be PR_F32 with dtype PR_BF16 (fp32 sums out of the reduce-scatter).
+ */
+typedef struct pr_adamw_args {
+    double lr, beta1, beta2, eps, weight_decay, grad_scale;
+    int64_t step;
+    int32_t numerics;
+    int32_t grad_dtype;  /* pr_dtype of g */
+} pr_adamw_args;
+
+int pr_adamw(void *p_dev, const void *g_dev, void *m_dev, void *v_dev, uint64_t n,
+             int dtype, const pr_adamw_args *args, void *stream);
+
+/* ---------------------------------------------------------------- K3: checkpoint -----
+ * PR-SUM64, the on-GPU checksum that stands in for hashlib.md5 over the file -- reference
+ * pyrecover/checkpoint.py:79-80 (save) and :162-163 (load).  The byte stream is read as
+ * little-endian u32 words w_i (tail zero-padded); mod 2^64:
+ *     A = sum w_i          B = sum (word_base + i + 1) * w_i
+ * sum_dev[0] += A, sum_dev[1] += B  (the caller zeroes sum_dev; partial sums over chunks
+ * taken with their own word_base add up to the sum of the whole).
+ */
+int pr_checksum(const void *data_dev, uint64_t nbytes, uint64_t word_base, uint64_t *sum_dev,
+                void *stream);
+
+/* A pack plan describes the static layout "n tensors -> one packed image": the role of
+ * model.state_dict() / optimizer.state_dict() feeding torch.save -- reference
+ * pyrecover/checkpoint.py:60-74 (vanilla) and :254-274 (torch.distributed.checkpoint).
+ * dst_off[i] must be a multiple of 16; bytes between segments are not written (keep the
+ * image zero-initialised).  The plan owns a small device table (scratch memory). */
+typedef struct pr_pack_plan pr_pack_plan;
+
+int pr_pack_plan_create(const void *const *tensor_dev, const uint64_t *nbytes,
+                        const uint64_t *dst_off, int n, uint64_t image_bytes,
+                        pr_pack_plan **plan_out);
+int pr_pack_plan_destroy(pr_pack_plan *plan);
+
+/* Gather every tensor of the plan into image (device memory, or mapped pinned host memory)
+ * and add PR-SUM64 of the packed image into sum_dev (2 x u64, zeroed by the caller; may be
+ * NULL to skip the checksum).  Replaces the per-storage synchronous D2H of torch.save --
+ * reference pyrecover/checkpoint.py:74. */
+int pr_ckpt_pack(const pr_pack_plan *plan, void *image, uint64_t *sum_dev, void *stream);
+
+/* Scatter the packed image back into the plan's tensors and add PR-SUM64 of the image
+ * into sum_dev: the role of torch.load + load_state_dict -- reference
+ * pyrecover/checkpoint.py:182-199 -- with the verification of :155-178 folded in. */
+int pr_ckpt_unpack(const pr_pack_plan *plan, const void *image, uint64_t *sum_dev,
+                   void *stream);
+
+/* Pinned, device-mapped host arena the snapshot lands in (replaces the pageable staging
+ * torch.save does implicitly -- reference pyrecover/checkpoint.py:74).  Zero-filled. */
+int pr_host_arena_alloc(uint64_t nbytes, void **host_ptr_out);
+int pr_host_arena_free(void *host_ptr);
+/* Device-visible alias of an arena pointer (for pr_ckpt_pack's direct-to-host mode). */
+int pr_host_arena_device_ptr(void *host_ptr, void **dev_ptr_out);
+/* Async copies in <= chunk_bytes pieces on `stream` (0 = one piece). */
+int pr_copy_d2h_async(void *dst_host, const void *src_dev, uint64_t nbytes,
+                      uint64_t chunk_bytes, void *stream);
+int pr_copy_h2d_async(void *dst_dev, const void *src_host, uint64_t nbytes,
+                      uint64_t chunk_bytes, void *stream);
+
+/* Native file writer: streams `n` (host pointer, length) pieces to `path + ".tmp"` with
+ * large write()s, fsyncs and renames to `path` -- the durable half of
+ * pyrecover/checkpoint.py:74 without the non-atomic in-place write.  Blocking; call it
+ * from a helper thread (it never touches the Python GIL). */
+int pr_file_write_atomic(const char *path, const void *const *pieces_host,
+                         const uint64_t *piece_bytes, int n, int do_fsync);
+
+/* ---------------------------------------------------------------- K1: allreduce ------
+ * Replaces the DDP Reducer's bucket allreduce -- reference train.py:110-115 (DDP ctor),
+ * firing inside loss.backward() at train.py:269: g <- sum_r g_r * (1/W) per flat bucket
+ * (torch/csrc/distributed/c10d/reducer.hpp:500).  One process per GPU; every rank maps
+ * every peer's symmetric regions and flag words over NVLink (CUDA IPC); the kernels pull
+ * 16-byte vectors from all peers, accumulate in fp32 in rank order 0..W-1 (every rank gets
+ * bit-identical results), scale, round once and push the result to every rank.
+ * NCCL/gloo are used only by the caller, to exchange the export blobs.
+ */
+typedef struct pr_comm pr_comm;
+
+int pr_comm_create(int rank, int world, pr_comm **comm_out);
+/* Emulated communicator: all `world` ranks live on the current device and one cooperative
+ * launch runs them side by side (single-GPU tests of the same kernels and flag protocol). */
+int pr_comm_create_emulated(int world, pr_comm **comm_out);
+int pr_comm_destroy(pr_comm *comm);
+/* Allocate symmetric region `region` (cudaMalloc, 256-B aligned, zero-filled). */
+int pr_comm_region_alloc(pr_comm *comm, int region, uint64_t nbytes);
+/* Local base pointer of a region (rank = the emulated rank, ignored for a real comm). */
+int pr_comm_region_ptr(pr_comm *comm, int region, int rank, void **dev_ptr_out);
+/* Write this rank's PR_EXPORT_BLOB_BYTES handle blob (after all regions are allocated). */
+int pr_comm_export(pr_comm *comm, void *blob_out);
+/* Import all ranks' blobs (world * PR_EXPORT_BLOB_BYTES, rank-major) and map the peers. */
+int pr_comm_import(pr_comm *comm, const void *blobs);
+/* 1 in *timed_out if a kernel of this communicator gave up waiting for a peer. */
+int pr_comm_error(pr_comm *comm, int *timed_out);
+
+typedef enum pr_ar_algo { PR_AR_AUTO = 0, PR_AR_ONE_SHOT = 1, PR_AR_TWO_SHOT = 2 } pr_ar_algo;
+
+/* In-place allreduce of region[offset, offset+nbytes) with result = round(sum * scale).
+ * offset and nbytes must be multiples of 16.  max_blocks bounds the grid (0 = one CTA per
+ * SM); every rank must pass identical arguments in the same order. */
+int pr_allreduce(pr_comm *comm, int region, uint64_t offset, uint64_t nbytes, int dtype,
+                 float scale, int algo, int max_blocks, void *stream);
+
+/* Fused reduce-scatter -> AdamW -> all-gather: rank r reduces slice r of the gradient
+ * region in fp32 registers, applies AdamW to slice r of (p, m, v) and pushes the updated
+ * parameters to every rank's parameter region.  Replaces train.py:269 + train.py:274 in
+ * one launch.  The moments live in two more symmetric regions of which a rank only ever
+ * touches its own slice (sharded optimizer state; pr_allgather_slices re-replicates them
+ * when a rank-0 checkpoint needs the whole).  n = elements, a multiple of 8; the gradient
+ * mean's 1/W goes in args->grad_scale; args->numerics must be 0. */
+int pr_allreduce_adamw(pr_comm *comm, int grad_region, int param_region, int m_region,
+                       int v_region, uint64_t elem_offset, uint64_t n, int dtype,
+                       const pr_adamw_args *args, int max_blocks, void *stream);
+
+/* All-gather of per-rank slices of a region (slice r of rank r -> every rank): used to
+ * re-replicate sharded moments before a rank-0 vanilla checkpoint (the reference's
+ * save_ckpt_vanilla writes the whole optimizer state from rank 0, checkpoint.py:58-74). */
+int pr_allgather_slices(pr_comm *comm, int region, uint64_t offset, uint64_t nbytes,
+                        int max_blocks, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PYRECOVER_B200_H */

@@ -1,0 +1,237 @@
+/*
+ * pr_oracle.c -- CPU restatement of the data-parallel hot path, TEST INFRASTRUCTURE ONLY.
+ *
+ * Nothing under oracle/ is part of the product: only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load this file's shared object, and
+ * only as the checker.  The product path (pyrecover_b200/) never imports it and has no CPU
+ * fallback.
+ *
+ * What it restates (reference = Shaswat-G/PyRecover; the arithmetic itself lives in the
+ * reference's un-pinned third-party dependency torch, see SURVEY.md section 8c -- the
+ * version this oracle is pinned against is torch 2.11.0):
+ *
+ *   orc_adamw_*        train.py:120-122 (AdamW ctor) + train.py:274 (optimizer.step()),
+ *                      i.e. torch/optim/adam.py:347-551 (_single_tensor_adam: wd :419,
+ *                      lerp :457, addcmul (next line), denom/addcdiv :541-547) and the
+ *                      fused kernel torch._fused_adamw_ (torch/optim/adam.py:803-900).
+ *   orc_allreduce_*    train.py:110-115 (DDP ctor) + train.py:269 (loss.backward()):
+ *                      g <- sum_r (g_r * 1/W) per flat bucket
+ *                      (torch/csrc/distributed/c10d/reducer.hpp:500 div_factor_).
+ *   orc_checksum64     replaces pyrecover/checkpoint.py:79-80,162-163 (md5 over the file):
+ *                      md5 is sequential by construction, so the path uses a position-
+ *                      weighted 2x64-bit sum that combines across chunks and ranks.
+ *   orc_pack           pyrecover/checkpoint.py:60-74 (state dict -> one byte stream).
+ *
+ * Pinning: tests/golden/ holds vectors produced by torch itself (scripts/make_golden.py,
+ * run in the build container where the reference and torch are importable);
+ * tests/test_oracle.py checks this file against them.
+ *
+ * Build: make -C oracle   (gcc -O2 -ffp-contract=off: no FMA contraction, so every float
+ * operation below is one IEEE-754 binary32 operation, exactly as the CUDA kernels issue
+ * them with __fmul_rn/__fadd_rn/__fmaf_rn/__fdiv_rn/__fsqrt_rn).
+ */
+#include <math.h>
+#include <stddef.h>
+#include <stdint.h>
+#include <string.h>
+
+typedef uint16_t bf16_t;
+
+static inline float bf2f(bf16_t h) {
+    uint32_t u = ((uint32_t)h) << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+/* round-to-nearest-even, NaN kept quiet: same as __float2bfloat16_rn / torch's c10::BFloat16 */
+static inline bf16_t f2bf(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (bf16_t)0x7fc0;
+    uint32_t lsb = (u >> 16) & 1u;
+    u += 0x7fffu + lsb;
+    return (bf16_t)(u >> 16);
+}
+
+static inline float rbf(float f) { return bf2f(f2bf(f)); }
+
+/* ------------------------------------------------------------------ AdamW ------------- */
+
+typedef struct {
+    float decay;        /* 1 - lr*wd                      */
+    float b1, omb1;     /* beta1, 1-beta1                 */
+    float b2, omb2;     /* beta2, 1-beta2                 */
+    float step_size;    /* lr / (1 - beta1^t)             */
+    float bc2_sqrt;     /* sqrt(1 - beta2^t)              */
+    float eps;
+    float gscale;       /* multiplies the gradient first (1/W of the DDP mean, or 1) */
+} orc_adamw_consts;
+
+/* Host-side scalar preparation, in double exactly like python's float arithmetic in
+ * torch/optim/adam.py:503-510, then narrowed once to binary32. */
+void orc_adamw_prepare(double lr, double beta1, double beta2, double eps, double wd,
+                       int64_t step, double gscale, orc_adamw_consts *c) {
+    double bc1 = 1.0 - pow(beta1, (double)step);
+    double bc2 = 1.0 - pow(beta2, (double)step);
+    c->decay = (float)(1.0 - lr * wd);
+    c->b1 = (float)beta1;
+    c->omb1 = (float)(1.0 - beta1);
+    c->b2 = (float)beta2;
+    c->omb2 = (float)(1.0 - beta2);
+    c->step_size = (float)(lr / bc1);
+    c->bc2_sqrt = (float)sqrt(bc2);
+    c->eps = (float)eps;
+    c->gscale = (float)gscale;
+}
+
+/* mode 0: fp32 op-math, one rounding at the store (the _fused_adamw_ numerics class).
+ * The operation forms (lerp with an fma for m, one fma for v, true division) are the ones
+ * torch 2.11's fused CPU kernel evaluates: with them this function is bit-identical to
+ * torch.optim.AdamW(fused=True) on CPU tensors over the golden vectors (tests/golden/). */
+static inline void adamw_elem_fp32(float *p, float g, float *m, float *v,
+                                   const orc_adamw_consts *c) {
+    g = g * c->gscale;
+    float pp = *p * c->decay;
+    float mm = fmaf(c->omb1, g - *m, *m);            /* lerp(m, g, 1-b1), |w|<0.5 branch */
+    float vv = fmaf(c->omb2 * g, g, *v * c->b2);      /* v*b2 + ((1-b2)*g)*g, one fma      */
+    float denom = sqrtf(vv) / c->bc2_sqrt + c->eps;
+    pp = pp - (c->step_size * mm) / denom;
+    *p = pp; *m = mm; *v = vv;
+}
+
+/* mode 1: every torch op of _single_tensor_adam rounds its result to the storage dtype
+ * (bf16).  Op order follows torch/optim/adam.py: mul_ (:419), lerp_ (:457), mul_+addcmul_,
+ * sqrt / div / add_ (:541-545), addcdiv_ (:547).  ATen's CPU lerp for |w|<0.5 is
+ * self + w*(end-self) evaluated with a fused multiply-add in the vectorised path, and its
+ * addcmul is fma(value*t1, t2, self); with those two forms this function is bit-identical
+ * to torch.optim.AdamW(fused=False) on CPU bf16 tensors over the golden vectors. */
+static inline void adamw_elem_stepwise(float *p, float g, float *m, float *v,
+                                       const orc_adamw_consts *c) {
+    if (c->gscale != 1.0f) g = rbf(g * c->gscale);
+    float pp = rbf(*p * c->decay);
+    float mm = rbf(fmaf(c->omb1, g - *m, *m));
+    float vv = rbf(*v * c->b2);
+    vv = rbf(fmaf(c->omb2 * g, g, vv));
+    float d = rbf(sqrtf(vv));
+    d = rbf(d / c->bc2_sqrt);
+    d = rbf(d + c->eps);
+    pp = rbf(pp + ((-c->step_size) * mm) / d);
+    *p = pp; *m = mm; *v = vv;
+}
+
+void orc_adamw_bf16(bf16_t *p, const bf16_t *g, bf16_t *m, bf16_t *v, size_t n,
+                    const orc_adamw_consts *c, int mode) {
+    for (size_t i = 0; i < n; ++i) {
+        float pf = bf2f(p[i]), mf = bf2f(m[i]), vf = bf2f(v[i]);
+        if (mode == 1) adamw_elem_stepwise(&pf, bf2f(g[i]), &mf, &vf, c);
+        else adamw_elem_fp32(&pf, bf2f(g[i]), &mf, &vf, c);
+        p[i] = f2bf(pf); m[i] = f2bf(mf); v[i] = f2bf(vf);
+    }
+}
+
+/* fp32 parameters / moments, gradient fp32 (the --model-dtype fp32 case, utils.py:176-181) */
+void orc_adamw_f32(float *p, const float *g, float *m, float *v, size_t n,
+                   const orc_adamw_consts *c) {
+    for (size_t i = 0; i < n; ++i) adamw_elem_fp32(&p[i], g[i], &m[i], &v[i], c);
+}
+
+/* bf16 p/m/v with an fp32 gradient (the fused reduce-scatter hands AdamW an fp32 sum) */
+void orc_adamw_bf16_gf32(bf16_t *p, const float *g, bf16_t *m, bf16_t *v, size_t n,
+                         const orc_adamw_consts *c) {
+    for (size_t i = 0; i < n; ++i) {
+        float pf = bf2f(p[i]), mf = bf2f(m[i]), vf = bf2f(v[i]);
+        adamw_elem_fp32(&pf, g[i], &mf, &vf, c);
+        p[i] = f2bf(pf); m[i] = f2bf(mf); v[i] = f2bf(vf);
+    }
+}
+
+/* ------------------------------------------------------------------ allreduce --------- */
+
+/* The product's semantics: accumulate the W contributions in binary32 in rank order
+ * 0..W-1, multiply by `scale` (1/W for the DDP mean), round once to bf16. */
+void orc_allreduce_bf16(const bf16_t *const *bufs, int world, size_t n, float scale,
+                        bf16_t *out) {
+    for (size_t i = 0; i < n; ++i) {
+        float acc = 0.0f;
+        for (int r = 0; r < world; ++r) acc = acc + bf2f(bufs[r][i]);
+        out[i] = f2bf(acc * scale);
+    }
+}
+
+/* fp32 result of the same sum (what the fused reduce-scatter keeps in registers). */
+void orc_allreduce_bf16_to_f32(const bf16_t *const *bufs, int world, size_t n, float scale,
+                               float *out) {
+    for (size_t i = 0; i < n; ++i) {
+        float acc = 0.0f;
+        for (int r = 0; r < world; ++r) acc = acc + bf2f(bufs[r][i]);
+        out[i] = acc * scale;
+    }
+}
+
+/* The reference's semantics (reducer pre-divides each rank's grad in bf16, the collective
+ * then sums bf16 values; the accumulation order/precision is NCCL's).  Restated with bf16
+ * accumulation in rank order -- the loosest member of the family, used by the tests to
+ * bound |ours - reference| ("Allreduce parity"). */
+void orc_allreduce_bf16_ddp(const bf16_t *const *bufs, int world, size_t n, bf16_t *out) {
+    float inv = 1.0f / (float)world;
+    for (size_t i = 0; i < n; ++i) {
+        float acc = rbf(bf2f(bufs[0][i]) * inv);
+        for (int r = 1; r < world; ++r) acc = rbf(acc + rbf(bf2f(bufs[r][i]) * inv));
+        out[i] = f2bf(acc);
+    }
+}
+
+void orc_allreduce_f32(const float *const *bufs, int world, size_t n, float scale, float *out) {
+    for (size_t i = 0; i < n; ++i) {
+        float acc = 0.0f;
+        for (int r = 0; r < world; ++r) acc = acc + bufs[r][i];
+        out[i] = acc * scale;
+    }
+}
+
+/* ------------------------------------------------------------------ checksum ---------- */
+
+/* PR-SUM64: the byte stream is read as little-endian u32 words w_0..w_{k-1} (the tail is
+ * zero-padded to a word).  With all arithmetic mod 2^64:
+ *     A = sum_i w_i                 B = sum_i (i + 1 + word_base) * w_i
+ * A chunk [o, o+k) therefore combines as  A += A_c ;  B += B_c  when the chunk was summed
+ * with word_base = o, which is what makes the sum computable by independent CTAs / ranks
+ * and lets a "checksum of checksums" be verified. */
+void orc_checksum64(const void *data, size_t nbytes, uint64_t word_base, uint64_t out[2]) {
+    const uint8_t *b = (const uint8_t *)data;
+    uint64_t A = 0, B = 0;
+    size_t nwords = nbytes / 4;
+    for (size_t i = 0; i < nwords; ++i) {
+        uint32_t w;
+        memcpy(&w, b + 4 * i, 4);
+        A += w;
+        B += (word_base + i + 1) * (uint64_t)w;
+    }
+    size_t rem = nbytes - 4 * nwords;
+    if (rem) {
+        uint32_t w = 0;
+        memcpy(&w, b + 4 * nwords, rem);
+        A += w;
+        B += (word_base + nwords + 1) * (uint64_t)w;
+    }
+    out[0] = A;
+    out[1] = B;
+}
+
+/* ------------------------------------------------------------------ pack -------------- */
+
+/* Gather n segments into dst at the given byte offsets (each a multiple of 16; gaps are
+ * zero-filled) and checksum the packed image [0, total_bytes).  Restates the role of
+ * state_dict() + torch.save's per-storage serialisation (pyrecover/checkpoint.py:60-74). */
+void orc_pack(const void *const *src, const uint64_t *nbytes, const uint64_t *dst_off, int n,
+              void *dst, uint64_t total_bytes, uint64_t out_sum[2]) {
+    memset(dst, 0, (size_t)total_bytes);
+    for (int s = 0; s < n; ++s) memcpy((uint8_t *)dst + dst_off[s], src[s], (size_t)nbytes[s]);
+    orc_checksum64(dst, (size_t)total_bytes, 0, out_sum);
+}
+
+void orc_unpack(const void *packed, const uint64_t *nbytes, const uint64_t *src_off, int n,
+                void *const *dst) {
+    for (int s = 0; s < n; ++s) memcpy(dst[s], (const uint8_t *)packed + src_off[s], (size_t)nbytes[s]);
+}
