@@ -16,45 +16,55 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kUnroll = 2;
 
+template <bool GRAD_F32>
+__device__ __forceinline__ void load_grad8(const void *g_, uint64_t j, float (&g)[8]) {
+    if (GRAD_F32) {
+        const uint4 *g4 = reinterpret_cast<const uint4 *>(g_) + 2 * j;
+        uint4 a = ld_stream_nc(g4), b = ld_stream_nc(g4 + 1);
+        g[0] = __uint_as_float(a.x); g[1] = __uint_as_float(a.y);
+        g[2] = __uint_as_float(a.z); g[3] = __uint_as_float(a.w);
+        g[4] = __uint_as_float(b.x); g[5] = __uint_as_float(b.y);
+        g[6] = __uint_as_float(b.z); g[7] = __uint_as_float(b.w);
+    } else {
+        unpack_bf8(ld_stream_nc(reinterpret_cast<const uint4 *>(g_) + j), g);
+    }
+}
+
 template <int NUMERICS, bool GRAD_F32>
 __global__ void __launch_bounds__(kThreads)
 adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__restrict__ m,
                   uint4 *__restrict__ v, uint64_t nvec, AdamWConsts c) {
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
-    for (; i < nvec; i += stride * kUnroll) {
+    // main loop: kUnroll full vectors per thread, all 4*kUnroll loads issued before any math
+    for (; i + (kUnroll - 1) * stride < nvec; i += stride * kUnroll) {
         uint4 P[kUnroll], M[kUnroll], V[kUnroll];
         float g[kUnroll][8];
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            uint64_t j = i + u * stride;
-            if (j < nvec) {
-                P[u] = ld_stream(p + j);
-                M[u] = ld_stream(m + j);
-                V[u] = ld_stream(v + j);
-                if (GRAD_F32) {
-                    const uint4 *g4 = reinterpret_cast<const uint4 *>(g_) + 2 * j;
-                    uint4 a = ld_stream_nc(g4), b = ld_stream_nc(g4 + 1);
-                    g[u][0] = __uint_as_float(a.x); g[u][1] = __uint_as_float(a.y);
-                    g[u][2] = __uint_as_float(a.z); g[u][3] = __uint_as_float(a.w);
-                    g[u][4] = __uint_as_float(b.x); g[u][5] = __uint_as_float(b.y);
-                    g[u][6] = __uint_as_float(b.z); g[u][7] = __uint_as_float(b.w);
-                } else {
-                    uint4 G = ld_stream_nc(reinterpret_cast<const uint4 *>(g_) + j);
-                    unpack_bf8(G, g[u]);
-                }
-            }
+            const uint64_t j = i + u * stride;
+            P[u] = ld_stream(p + j);
+            M[u] = ld_stream(m + j);
+            V[u] = ld_stream(v + j);
+            load_grad8<GRAD_F32>(g_, j, g[u]);
         }
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-            uint64_t j = i + u * stride;
-            if (j < nvec) {
-                adamw_vec8<NUMERICS>(P[u], g[u], M[u], V[u], c);
-                st_stream(p + j, P[u]);
-                st_stream(m + j, M[u]);
-                st_stream(v + j, V[u]);
-            }
+            const uint64_t j = i + u * stride;
+            adamw_vec8<NUMERICS>(P[u], g[u], M[u], V[u], c);
+            st_stream(p + j, P[u]);
+            st_stream(m + j, M[u]);
+            st_stream(v + j, V[u]);
         }
+    }
+    for (; i < nvec; i += stride) {
+        uint4 P = ld_stream(p + i), M = ld_stream(m + i), V = ld_stream(v + i);
+        float g[8];
+        load_grad8<GRAD_F32>(g_, i, g);
+        adamw_vec8<NUMERICS>(P, g, M, V, c);
+        st_stream(p + i, P);
+        st_stream(m + i, M);
+        st_stream(v + i, V);
     }
 }
 

@@ -1,0 +1,254 @@
+"""Tensor-level wrappers over the C ABI (include/pyrecover_b200.h).
+
+Everything here takes torch CUDA tensors only for their device pointers and the current
+stream; the arithmetic is in the sm_100a kernels.  CPU tensors are rejected: there is no
+CPU fallback on the product path.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_int, c_uint64, c_void_p
+from typing import Optional, Sequence
+
+import torch
+
+from . import _lib
+from ._lib import AdamWArgs, check, dtype_code, lib, stream_ptr
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if not t.is_cuda:
+            raise RuntimeError("pyrecover_b200 kernels need CUDA tensors (no CPU fallback)")
+        if not t.is_contiguous():
+            raise RuntimeError("pyrecover_b200 kernels need contiguous tensors")
+
+
+def device_info():
+    sm, major, minor = c_int(), c_int(), c_int()
+    check(lib().pr_device_info(ctypes.byref(sm), ctypes.byref(major), ctypes.byref(minor)), "pr_device_info")
+    return sm.value, major.value, minor.value
+
+
+# ------------------------------------------------------------------------- K2 AdamW -----
+
+def adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, numerics=0,
+               grad_dtype=_lib.PR_BF16) -> AdamWArgs:
+    return AdamWArgs(float(lr), float(beta1), float(beta2), float(eps), float(weight_decay),
+                     float(grad_scale), int(step), int(numerics), int(grad_dtype))
+
+
+def adamw_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, *, lr: float,
+           beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, weight_decay: float = 0.01,
+           step: int = 1, grad_scale: float = 1.0, numerics: int = 0, stream=None) -> None:
+    """One flat AdamW update, in place on p, m, v (reference train.py:274)."""
+    _require_cuda(p, g, m, v)
+    n = p.numel()
+    if not (g.numel() == n and m.numel() == n and v.numel() == n):
+        raise ValueError("p, g, m, v must have the same number of elements")
+    if m.dtype != p.dtype or v.dtype != p.dtype:
+        raise TypeError("m and v must have the dtype of p")
+    a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, dtype_code(g.dtype))
+    check(lib().pr_adamw(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, dtype_code(p.dtype),
+                         ctypes.byref(a), stream_ptr(stream)), "pr_adamw")
+
+
+# ------------------------------------------------------------------------- K3 checksum --
+
+def checksum_into(t: torch.Tensor, sum_dev: torch.Tensor, word_base: int = 0, stream=None) -> None:
+    """sum_dev (2 x int64 on the device, zeroed by the caller) += PR-SUM64(t's bytes)."""
+    _require_cuda(t, sum_dev)
+    assert sum_dev.dtype == torch.int64 and sum_dev.numel() == 2
+    check(lib().pr_checksum(t.data_ptr(), t.numel() * t.element_size(), word_base, sum_dev.data_ptr(),
+                            stream_ptr(stream)), "pr_checksum")
+
+
+def _sum_to_ints(sum_dev: torch.Tensor):
+    a, b = sum_dev.tolist()
+    return a & (2**64 - 1), b & (2**64 - 1)
+
+
+def checksum(t: torch.Tensor, word_base: int = 0):
+    """PR-SUM64 of a CUDA tensor's bytes -> (A, B) python ints (synchronises)."""
+    s = torch.zeros(2, dtype=torch.int64, device=t.device)
+    checksum_into(t, s, word_base)
+    return _sum_to_ints(s)
+
+
+class PackPlan:
+    """Static layout: n CUDA tensors -> one packed image (pr_pack_plan)."""
+
+    def __init__(self, tensors: Sequence[torch.Tensor], offsets: Sequence[int], image_bytes: int):
+        _require_cuda(*tensors)
+        self.tensors = list(tensors)          # keeps the memory alive
+        self.offsets = [int(o) for o in offsets]
+        self.nbytes = [t.numel() * t.element_size() for t in tensors]
+        self.image_bytes = int(image_bytes)
+        n = len(tensors)
+        ptrs = (c_void_p * n)(*[t.data_ptr() for t in tensors])
+        lens = (c_uint64 * n)(*self.nbytes)
+        offs = (c_uint64 * n)(*self.offsets)
+        self._h = c_void_p()
+        check(lib().pr_pack_plan_create(ptrs, lens, offs, n, self.image_bytes, ctypes.byref(self._h)),
+              "pr_pack_plan_create")
+
+    def pack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None) -> None:
+        check(lib().pr_ckpt_pack(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
+                                 stream_ptr(stream)), "pr_ckpt_pack")
+
+    def unpack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None) -> None:
+        check(lib().pr_ckpt_unpack(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
+                                   stream_ptr(stream)), "pr_ckpt_unpack")
+
+    def close(self) -> None:
+        if self._h:
+            lib().pr_pack_plan_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class HostArena:
+    """Pinned, device-mapped, zero-filled host buffer (pr_host_arena_*)."""
+
+    def __init__(self, nbytes: int):
+        self.nbytes = int(nbytes)
+        p = c_void_p()
+        check(lib().pr_host_arena_alloc(self.nbytes, ctypes.byref(p)), "pr_host_arena_alloc")
+        self.ptr = p.value or 0
+        self._buf = (ctypes.c_char * self.nbytes).from_address(self.ptr) if self.nbytes else None
+
+    def view(self, offset: int = 0, nbytes: Optional[int] = None) -> memoryview:
+        nbytes = self.nbytes - offset if nbytes is None else nbytes
+        return memoryview(self._buf).cast("B")[offset:offset + nbytes]
+
+    def device_ptr(self) -> int:
+        d = c_void_p()
+        check(lib().pr_host_arena_device_ptr(self.ptr, ctypes.byref(d)), "pr_host_arena_device_ptr")
+        return d.value
+
+    def close(self) -> None:
+        if self.ptr:
+            self._buf = None
+            check(lib().pr_host_arena_free(self.ptr), "pr_host_arena_free")
+            self.ptr = 0
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def copy_d2h_async(dst_host_ptr: int, src: torch.Tensor, nbytes: int, chunk_bytes: int = 0, stream=None):
+    check(lib().pr_copy_d2h_async(dst_host_ptr, src.data_ptr(), nbytes, chunk_bytes, stream_ptr(stream)),
+          "pr_copy_d2h_async")
+
+
+def copy_h2d_async(dst: torch.Tensor, src_host_ptr: int, nbytes: int, chunk_bytes: int = 0, stream=None):
+    check(lib().pr_copy_h2d_async(dst.data_ptr(), src_host_ptr, nbytes, chunk_bytes, stream_ptr(stream)),
+          "pr_copy_h2d_async")
+
+
+def file_write_atomic(path: str, pieces: Sequence[tuple], fsync: bool = True) -> None:
+    """pieces: (host_ptr, nbytes) pairs written back to back to `path` (tmp + rename)."""
+    n = len(pieces)
+    ptrs = (c_void_p * n)(*[p for p, _ in pieces])
+    lens = (c_uint64 * n)(*[b for _, b in pieces])
+    check(lib().pr_file_write_atomic(str(path).encode(), ptrs, lens, n, 1 if fsync else 0),
+          "pr_file_write_atomic")
+
+
+# ------------------------------------------------------------------------- K1 comm ------
+
+class _DevMem:
+    """__cuda_array_interface__ holder so torch can view library-owned device memory."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2, "strides": None}
+
+
+def tensor_from_ptr(ptr: int, nbytes: int, dtype: torch.dtype, device, owner=None) -> torch.Tensor:
+    t = torch.as_tensor(_DevMem(ptr, nbytes, owner), device=device)
+    return t.view(dtype)
+
+
+class Comm:
+    """P2P communicator (pr_comm).  `pg` is a torch.distributed group used ONLY to exchange
+    the IPC export blobs (bootstrap); emulated=True runs all ranks on the current device."""
+
+    def __init__(self, rank: int = 0, world: int = 1, emulated: bool = False):
+        self.rank, self.world, self.emulated = rank, world, emulated
+        self._h = c_void_p()
+        if emulated:
+            check(lib().pr_comm_create_emulated(world, ctypes.byref(self._h)), "pr_comm_create_emulated")
+        else:
+            check(lib().pr_comm_create(rank, world, ctypes.byref(self._h)), "pr_comm_create")
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self.region_bytes = {}
+
+    def alloc_region(self, region: int, nbytes: int) -> None:
+        check(lib().pr_comm_region_alloc(self._h, region, nbytes), "pr_comm_region_alloc")
+        self.region_bytes[region] = nbytes
+
+    def region_tensor(self, region: int, dtype: torch.dtype, rank: int = 0) -> torch.Tensor:
+        p = c_void_p()
+        check(lib().pr_comm_region_ptr(self._h, region, rank, ctypes.byref(p)), "pr_comm_region_ptr")
+        return tensor_from_ptr(p.value, self.region_bytes[region], dtype, self.device, owner=self)
+
+    def connect(self, pg=None) -> None:
+        """Exchange export blobs over torch.distributed (bootstrap only) and map the peers."""
+        if self.emulated or self.world == 1:
+            if not self.emulated:
+                blob = ctypes.create_string_buffer(_lib.PR_EXPORT_BLOB_BYTES)
+                check(lib().pr_comm_export(self._h, blob), "pr_comm_export")
+                check(lib().pr_comm_import(self._h, blob), "pr_comm_import")
+            return
+        import torch.distributed as dist
+        blob = ctypes.create_string_buffer(_lib.PR_EXPORT_BLOB_BYTES)
+        check(lib().pr_comm_export(self._h, blob), "pr_comm_export")
+        mine = torch.frombuffer(bytearray(blob.raw), dtype=torch.uint8)
+        backend = dist.get_backend(pg)
+        dev = self.device if "nccl" in str(backend) else torch.device("cpu")
+        mine = mine.to(dev)
+        gathered = [torch.empty_like(mine) for _ in range(self.world)]
+        dist.all_gather(gathered, mine, group=pg)
+        allb = b"".join(bytes(t.cpu().numpy().tobytes()) for t in gathered)
+        check(lib().pr_comm_import(self._h, allb), "pr_comm_import")
+
+    def allreduce(self, region: int, offset: int, nbytes: int, dtype: torch.dtype, scale: float,
+                  algo: int = _lib.PR_AR_AUTO, max_blocks: int = 0, stream=None) -> None:
+        check(lib().pr_allreduce(self._h, region, offset, nbytes, dtype_code(dtype), scale, algo,
+                                 max_blocks, stream_ptr(stream)), "pr_allreduce")
+
+    def allreduce_adamw(self, grad_region: int, param_region: int, m_region: int, v_region: int,
+                        elem_offset: int, n: int, args: AdamWArgs, max_blocks: int = 0, stream=None) -> None:
+        check(lib().pr_allreduce_adamw(self._h, grad_region, param_region, m_region, v_region, elem_offset,
+                                       n, _lib.PR_BF16, ctypes.byref(args), max_blocks, stream_ptr(stream)),
+              "pr_allreduce_adamw")
+
+    def allgather_slices(self, region: int, offset: int, nbytes: int, max_blocks: int = 0, stream=None):
+        check(lib().pr_allgather_slices(self._h, region, offset, nbytes, max_blocks, stream_ptr(stream)),
+              "pr_allgather_slices")
+
+    def timed_out(self) -> bool:
+        e = c_int()
+        check(lib().pr_comm_error(self._h, ctypes.byref(e)), "pr_comm_error")
+        return bool(e.value)
+
+    def close(self) -> None:
+        if self._h:
+            lib().pr_comm_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

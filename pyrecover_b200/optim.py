@@ -1,0 +1,165 @@
+"""B200AdamW -- drop-in for `torch.optim.AdamW(model.parameters(), lr=..., fused=...)`.
+
+Replaces the optimizer the reference builds at train.py:120-122 and steps at train.py:274.
+It honours the torch.optim.Optimizer protocol that the rest of the reference consumes:
+`param_groups` (mutated by LambdaLR, utils.py:59-81 / train.py:275), `zero_grad()`
+(train.py:260), `state_dict()/load_state_dict()` (pyrecover/checkpoint.py:69,188), with a
+state dict that is key-for-key what torch.optim.AdamW produces, so checkpoints interchange
+with the reference in both directions.
+
+What changes underneath: parameters, gradients and both moments live in flat HBM arenas
+(flat.FlatArena) and one K2 launch (csrc/adamw.cu) updates a whole param group.  With a
+GradSync attached (world > 1) the gradient arena is the NVLink communication buffer of K1
+and `step()` can run the fused reduce-scatter -> AdamW -> all-gather kernel instead.
+
+`fused` keeps the reference flag's meaning as a NUMERICS selector: fused=True -> fp32
+op-math rounded once (class of torch._fused_adamw_), fused=False/None -> every torch op's
+result rounded to the storage dtype (class of _single_tensor_adam, the reference default).
+Both are a single launch here.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, Iterable, List, Optional
+
+import torch
+
+from . import kernels as K
+from .flat import FlatArena
+
+
+class B200AdamW(torch.optim.Optimizer):
+    def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2, amsgrad: bool = False, *, maximize: bool = False,
+                 foreach: Optional[bool] = None, capturable: bool = False, differentiable: bool = False,
+                 fused: Optional[bool] = None, numerics: Optional[int] = None, grad_sync=None):
+        if amsgrad or maximize or capturable or differentiable:
+            raise NotImplementedError("B200AdamW implements the reference configuration only "
+                                      "(amsgrad/maximize/capturable/differentiable = False)")
+        if isinstance(lr, torch.Tensor):
+            lr = float(lr)
+        if lr < 0 or eps < 0 or not (0 <= betas[0] < 1) or not (0 <= betas[1] < 1) or weight_decay < 0:
+            raise ValueError("invalid AdamW hyper-parameter")
+        self._numerics_override = numerics
+        self._grad_sync = grad_sync
+        self._arenas: List[FlatArena] = []
+        self._steps: List[int] = []
+        self._step_tensors: List[torch.Tensor] = []
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad,
+                        maximize=maximize, foreach=foreach, capturable=capturable,
+                        differentiable=differentiable, fused=fused, decoupled_weight_decay=True)
+        super().__init__(params, defaults)
+
+    # ------------------------------------------------------------------ construction ----
+    def add_param_group(self, param_group: Dict[str, Any]) -> None:
+        super().add_param_group(param_group)
+        group = self.param_groups[-1]
+        params = group["params"]
+        if self._grad_sync is not None:
+            if self._arenas:
+                raise NotImplementedError("GradSync supports a single param group (as the reference uses)")
+            arena = FlatArena(params, world=self._grad_sync.world, alloc=self._grad_sync.alloc)
+            self._grad_sync.attach(arena)
+        else:
+            arena = FlatArena(params)
+        self._arenas.append(arena)
+        self._steps.append(0)
+        # one shared scalar per group: every parameter of the reference steps in lock-step
+        step_t = torch.zeros((), dtype=torch.float32)
+        self._step_tensors.append(step_t)
+        for q, mv, vv in zip(params, arena.m_views, arena.v_views):
+            # eager state (torch creates it lazily at the first step -- adam.py:168-184 -- which is
+            # why a DCP resume into a fresh reference optimizer silently drops the moments)
+            self.state[q] = {"step": step_t, "exp_avg": mv, "exp_avg_sq": vv}
+
+    @property
+    def arenas(self) -> List[FlatArena]:
+        return self._arenas
+
+    def _numerics(self, group) -> int:
+        if self._numerics_override is not None:
+            return int(self._numerics_override)
+        if self._arenas[0].dtype != torch.bfloat16:
+            return 0
+        return 0 if group.get("fused") else 1
+
+    # ------------------------------------------------------------------ step -------------
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for gi, group in enumerate(self.param_groups):
+            arena = self._arenas[gi]
+            beta1, beta2 = group["betas"]
+            lr = float(group["lr"])
+            if self._grad_sync is not None:
+                if not self._grad_sync.grads_ready():
+                    continue
+                self._steps[gi] += 1
+                self._step_tensors[gi].fill_(self._steps[gi])
+                self._grad_sync.reduce_and_step(
+                    lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"], weight_decay=group["weight_decay"],
+                    step=self._steps[gi], numerics=self._numerics(group))
+                continue
+            have = [q.grad is not None for q in arena.params]
+            if not any(have):
+                continue
+            if not all(have):
+                raise RuntimeError("B200AdamW: some parameters have no gradient; the flat arena updates "
+                                   "all parameters of a group together (reference: find_unused_parameters=False)")
+            arena.gather_grads()
+            self._steps[gi] += 1
+            self._step_tensors[gi].fill_(self._steps[gi])
+            K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
+                     weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group))
+        return loss
+
+    # ------------------------------------------------------------------ state dict -------
+    def state_dict(self) -> Dict[str, Any]:
+        if self._grad_sync is not None:
+            self._grad_sync.replicate_moments()
+        sd = super().state_dict()
+        # torch.optim.AdamW hands out one scalar per parameter; give each entry its own tensor
+        for st in sd["state"].values():
+            st["step"] = st["step"].clone()
+        return sd
+
+    @torch.no_grad()
+    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+        groups = state_dict["param_groups"]
+        if len(groups) != len(self.param_groups):
+            raise ValueError("loaded state dict has a different number of parameter groups")
+        state = state_dict.get("state", {})
+        for gi, (group, saved) in enumerate(zip(self.param_groups, groups)):
+            if len(saved["params"]) != len(group["params"]):
+                raise ValueError("loaded state dict contains a parameter group that doesn't match the size of "
+                                 "optimizer's group")
+            arena = self._arenas[gi]
+            step_val = None
+            for slot, idx in enumerate(saved["params"]):
+                st = state.get(idx, state.get(str(idx)))
+                if st is None:
+                    continue     # torch semantics: parameter never stepped
+                arena.m_views[slot].copy_(st["exp_avg"].to(arena.device, arena.dtype).view_as(arena.m_views[slot]))
+                arena.v_views[slot].copy_(st["exp_avg_sq"].to(arena.device, arena.dtype).view_as(arena.v_views[slot]))
+                s = float(st["step"]) if not torch.is_tensor(st["step"]) else float(st["step"].item())
+                if step_val is not None and s != step_val:
+                    raise ValueError("B200AdamW: parameters of one group carry different step counts")
+                step_val = s
+            if step_val is None:      # empty state: fresh optimizer
+                step_val = 0.0
+                arena.m.zero_()
+                arena.v.zero_()
+            self._steps[gi] = int(step_val)
+            self._step_tensors[gi].fill_(step_val)
+            for k, val in saved.items():
+                if k != "params":
+                    group[k] = val
+        if self._grad_sync is not None:
+            self._grad_sync.moments_loaded()
+
+    def set_step(self, group_index: int, step: int) -> None:
+        """Used by the fast checkpoint loader, which restores the arenas with the unpack kernel."""
+        self._steps[group_index] = int(step)
+        self._step_tensors[group_index].fill_(float(step))

@@ -1,0 +1,115 @@
+#!/usr/bin/env python
+"""Single-GPU micro-benchmarks of K2 (AdamW), K3 (checksum / pack) against the HBM roofline
+and the torch incumbents.  CUDA-event timing, L2 flushed by size (all arenas >> 126 MB).
+Usage: python scripts/microbench.py [--n-log2 30] [--iters 10] [--json out.json]"""
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from pyrecover_b200 import kernels as K  # noqa: E402
+
+
+def timeit(fn, iters, warmup=3):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for a, b in evs:
+        a.record()
+        fn()
+        b.record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--n-log2", type=int, default=30)
+    ap.add_argument("--iters", type=int, default=10)
+    ap.add_argument("--json", type=str, default=None)
+    a = ap.parse_args()
+    n = 1 << a.n_log2
+    peaks = {}
+    pk = Path(__file__).resolve().parents[1] / "MEASURED_PEAKS.json"
+    if pk.exists():
+        peaks = json.loads(pk.read_text())
+    hbm = peaks.get("hbm_gbs", 6650.0)
+    res = {"n": n, "hbm_peak_gbs": hbm, "device": torch.cuda.get_device_name()}
+    dev = "cuda"
+    p = (torch.randn(n, device=dev) * 0.02).bfloat16()
+    g = (torch.randn(n, device=dev) * 1e-3).bfloat16()
+    m = torch.zeros_like(p)
+    v = torch.zeros_like(p)
+
+    def row(name, ms, best, nbytes):
+        gbs = nbytes / ms / 1e6
+        res[name] = {"ms_median": ms, "ms_best": best, "gbs": gbs, "frac_of_measured_hbm": gbs / hbm}
+        print(f"{name:34s} {ms:9.3f} ms (best {best:9.3f})  {gbs:8.1f} GB/s  {gbs / hbm:6.3f} of measured HBM copy")
+
+    # plain copy for reference (the denominators' own method)
+    ms, best = timeit(lambda: m.copy_(p), a.iters)
+    row("torch copy_ (2 B/elt r+w)", ms, best, 4 * n)
+    m.zero_()
+    for numerics in (0, 1):
+        step = [0]
+
+        def f():
+            step[0] += 1
+            K.adamw_(p, g, m, v, lr=1e-5, step=step[0], numerics=numerics)
+        ms, best = timeit(f, a.iters)
+        row(f"pr_adamw bf16 numerics={numerics}", ms, best, 14 * n)
+    # torch incumbents on the same flat tensor and on a 291-tensor split
+    P = torch.nn.Parameter(p.clone())
+    P.grad = g
+    for fused in (True, False):
+        opt = torch.optim.AdamW([P], lr=1e-5, fused=fused)
+        ms, best = timeit(opt.step, a.iters)
+        row(f"torch AdamW flat fused={fused}", ms, best, 14 * n)
+        del opt
+    del P
+    torch.cuda.empty_cache()
+    chunks = list(torch.split(p.clone(), n // 291 + 1))
+    params = [torch.nn.Parameter(c) for c in chunks]
+    for q, gg in zip(params, torch.split(g, n // 291 + 1)):
+        q.grad = gg
+    opt = torch.optim.AdamW(params, lr=1e-5, fused=True)
+    ms, best = timeit(opt.step, a.iters)
+    row("torch AdamW 291 tensors fused=True", ms, best, 14 * n)
+    del opt, params, chunks
+    torch.cuda.empty_cache()
+
+    # checksum / pack
+    s = torch.zeros(2, dtype=torch.int64, device=dev)
+    ms, best = timeit(lambda: K.checksum_into(p, s), a.iters)
+    row("pr_checksum (1 B/B read)", ms, best, 2 * n)
+    chunk = (n // 291 + 127) // 128 * 128      # 256-B aligned tensor starts, like the flat arena
+    views = list(torch.split(p, chunk)) + list(torch.split(m, chunk)) + list(torch.split(v, chunk))
+    offs, cur = [], 0
+    for t in views:
+        offs.append(cur)
+        cur += (t.numel() * 2 + 255) // 256 * 256
+    image = torch.zeros(cur, dtype=torch.uint8, device=dev)
+    plan = K.PackPlan(views, offs, cur)
+    ms, best = timeit(lambda: plan.pack(image.data_ptr(), s), a.iters)
+    row("pr_ckpt_pack p+m+v (+sum)", ms, best, 2 * 6 * n)
+    ms, best = timeit(lambda: plan.pack(image.data_ptr(), None), a.iters)
+    row("pr_ckpt_pack p+m+v (no sum)", ms, best, 2 * 6 * n)
+    ms, best = timeit(lambda: plan.unpack(image.data_ptr(), s), a.iters)
+    row("pr_ckpt_unpack p+m+v (+sum)", ms, best, 2 * 6 * n)
+    # D2H of the image into the pinned arena (PCIe leg)
+    arena = K.HostArena(cur)
+    ms, best = timeit(lambda: K.copy_d2h_async(arena.ptr, image, cur, 64 << 20), 3, warmup=1)
+    res["d2h_pinned"] = {"ms_median": ms, "gbs": cur / ms / 1e6}
+    print(f"{'D2H image -> pinned arena':34s} {ms:9.3f} ms  {cur / ms / 1e6:8.1f} GB/s (PCIe)")
+    if a.json:
+        Path(a.json).parent.mkdir(parents=True, exist_ok=True)
+        Path(a.json).write_text(json.dumps(res, indent=1))
+
+
+if __name__ == "__main__":
+    main()
