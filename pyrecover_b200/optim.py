@@ -89,6 +89,10 @@ class B200AdamW(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        fence = getattr(self, "_snapshot_fence", None)
+        if fence is not None:      # a direct-mode checkpoint is still reading the live arenas
+            torch.cuda.current_stream().wait_event(fence)
+            self._snapshot_fence = None
         for gi, group in enumerate(self.param_groups):
             arena = self._arenas[gi]
             beta1, beta2 = group["betas"]
@@ -121,12 +125,14 @@ class B200AdamW(torch.optim.Optimizer):
             self._grad_sync.replicate_moments()
         sd = super().state_dict()
         # torch.optim.AdamW hands out one scalar per parameter; give each entry its own tensor
-        for st in sd["state"].values():
-            st["step"] = st["step"].clone()
+        sd["state"] = {k: {**st, "step": st["step"].clone()} for k, st in sd["state"].items()}
         return sd
 
     @torch.no_grad()
-    def load_state_dict(self, state_dict: Dict[str, Any]) -> None:
+    def load_state_dict(self, state_dict: Dict[str, Any], tensors_restored: bool = False) -> None:
+        """torch.optim.Optimizer.load_state_dict semantics.  tensors_restored=True (used by the
+        fast checkpoint loader) means the unpack kernel already put exp_avg / exp_avg_sq into the
+        arenas: only hyper-parameters and the step count are taken from the dict."""
         groups = state_dict["param_groups"]
         if len(groups) != len(self.param_groups):
             raise ValueError("loaded state dict has a different number of parameter groups")
@@ -141,16 +147,18 @@ class B200AdamW(torch.optim.Optimizer):
                 st = state.get(idx, state.get(str(idx)))
                 if st is None:
                     continue     # torch semantics: parameter never stepped
-                arena.m_views[slot].copy_(st["exp_avg"].to(arena.device, arena.dtype).view_as(arena.m_views[slot]))
-                arena.v_views[slot].copy_(st["exp_avg_sq"].to(arena.device, arena.dtype).view_as(arena.v_views[slot]))
+                if not tensors_restored:
+                    arena.m_views[slot].copy_(st["exp_avg"].to(arena.device, arena.dtype).view_as(arena.m_views[slot]))
+                    arena.v_views[slot].copy_(st["exp_avg_sq"].to(arena.device, arena.dtype).view_as(arena.v_views[slot]))
                 s = float(st["step"]) if not torch.is_tensor(st["step"]) else float(st["step"].item())
                 if step_val is not None and s != step_val:
                     raise ValueError("B200AdamW: parameters of one group carry different step counts")
                 step_val = s
             if step_val is None:      # empty state: fresh optimizer
                 step_val = 0.0
-                arena.m.zero_()
-                arena.v.zero_()
+                if not tensors_restored:
+                    arena.m.zero_()
+                    arena.v.zero_()
             self._steps[gi] = int(step_val)
             self._step_tensors[gi].fill_(step_val)
             for k, val in saved.items():

@@ -1,0 +1,488 @@
+"""Checkpoint snapshot engine: device-side pack + checksum -> pinned host arena -> writer thread.
+
+Replaces the body of the reference's save path (pyrecover/checkpoint.py:58-84: state_dict ->
+torch.save with one synchronous pageable D2H per storage -> re-read of the whole file for md5,
+all on rank 0 while training is stopped; and :254-274, torch.distributed.checkpoint) and of its
+load path (:182-199, :352-356).
+
+Timeline of one save:
+
+    training stream : ... optimizer.step | K3 pack+checksum (HBM->HBM, ~ms) | next forward ...
+    side stream     :                     wait E1 | D2H image -> pinned arena (PCIe) | E2
+    writer thread   :                                        wait E2 | file write, fsync,
+                                                             rename, side-cars, rotation
+
+`save_*` returns once the pack kernel and the copies are ENQUEUED: the snapshot is consistent
+(stream order puts the pack between this step's optimizer update and the next one), the
+training stream is only occupied for the pack kernel, and durability is awaited by the next
+save / load / `wait()`.
+
+Two images exist per (model, optimizer): the FULL image (vanilla .pt file: p | m | v arenas +
+stray tensors, one record per dtype) and the SHARD image (sharded directory format: this rank's
+1/W element slice of p, m and v).  Each owns its pack plan, HBM staging buffer and pinned arena,
+created on first use.
+"""
+from __future__ import annotations
+
+import copy
+import json
+import os
+import re
+import threading
+import time
+from collections import OrderedDict
+from pathlib import Path
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+
+from . import kernels as K
+from . import ptfile as PT
+
+ALIGN = 256
+COPY_CHUNK = 64 << 20
+_M64 = (1 << 64) - 1
+SHARD_FORMAT = 1
+
+
+def _round_up(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+class Piece:
+    """A contiguous run of device bytes and where it sits in an image."""
+    __slots__ = ("tensor", "img_off", "nbytes", "record", "rec_off", "global_off")
+
+    def __init__(self, tensor: torch.Tensor, img_off: int, record: str = "", rec_off: int = 0,
+                 global_off: int = 0):
+        self.tensor = tensor
+        self.img_off = img_off
+        self.nbytes = tensor.numel() * tensor.element_size()
+        self.record, self.rec_off, self.global_off = record, rec_off, global_off
+
+
+class Image:
+    """pack plan + staging + pinned arena + checksum words for one list of pieces."""
+
+    def __init__(self, pieces: Sequence[Piece], image_bytes: int, device: torch.device, staged: bool):
+        self.pieces = list(pieces)
+        self.image_bytes = max(int(image_bytes), ALIGN)
+        self.device = device
+        self.plan = K.PackPlan([p.tensor for p in self.pieces], [p.img_off for p in self.pieces], self.image_bytes)
+        self.staging = torch.zeros(self.image_bytes, dtype=torch.uint8, device=device) if staged else None
+        self.host = K.HostArena(self.image_bytes)
+        self.sum_dev = torch.zeros(2, dtype=torch.int64, device=device)
+        self.sum_host = torch.zeros(2, dtype=torch.int64).pin_memory()
+        self.e_copied: Optional[torch.cuda.Event] = None
+
+    def stage(self, side: torch.cuda.Stream) -> torch.cuda.Event:
+        """Pack (+PR-SUM64) on the current stream, D2H on `side`.  Returns the copy-done event."""
+        main = torch.cuda.current_stream(self.device)
+        if self.e_copied is not None:
+            main.wait_event(self.e_copied)      # the staging image may still be draining
+        self.sum_dev.zero_()
+        e_packed = torch.cuda.Event()
+        if self.staging is not None:
+            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=main)
+            e_packed.record(main)
+            side.wait_event(e_packed)
+            K.copy_d2h_async(self.host.ptr, self.staging, self.image_bytes, COPY_CHUNK, stream=side)
+        else:                                    # direct: copy engines read the live tensors
+            e_packed.record(main)
+            side.wait_event(e_packed)
+            for p in self.pieces:
+                if p.nbytes:
+                    K.checksum_into(p.tensor.reshape(-1), self.sum_dev, p.img_off // 4, stream=side)
+                    K.copy_d2h_async(self.host.ptr + p.img_off, p.tensor, p.nbytes, COPY_CHUNK, stream=side)
+        with torch.cuda.stream(side):
+            self.sum_host.copy_(self.sum_dev, non_blocking=True)
+        e = torch.cuda.Event()
+        e.record(side)
+        self.e_copied = e
+        return e
+
+    def checksum(self) -> Tuple[int, int]:
+        a, b = self.sum_host.tolist()
+        return a & _M64, b & _M64
+
+    def restore(self) -> Tuple[int, int]:
+        """pinned arena -> HBM -> unpack into the live tensors; returns PR-SUM64 of the image."""
+        main = torch.cuda.current_stream(self.device)
+        image = self.staging if self.staging is not None else \
+            torch.empty(self.image_bytes, dtype=torch.uint8, device=self.device)
+        K.copy_h2d_async(image, self.host.ptr, self.image_bytes, COPY_CHUNK, stream=main)
+        self.sum_dev.zero_()
+        self.plan.unpack(image.data_ptr(), self.sum_dev, stream=main)
+        self._last_image = image
+        return K._sum_to_ints(self.sum_dev)
+
+    def close(self) -> None:
+        self.plan.close()
+        self.host.close()
+
+
+class Snapshotter:
+    """Checkpoint engine for one (model, B200AdamW) pair; layouts are static for the job."""
+
+    def __init__(self, model: torch.nn.Module, optimizer, mode: Optional[str] = None):
+        self.module = model.module if hasattr(model, "module") else model
+        self.optimizer = optimizer
+        self.mode = mode or os.environ.get("PYRECOVER_B200_SNAPSHOT", "staged")
+        if self.mode not in ("staged", "direct"):
+            raise ValueError("snapshot mode must be 'staged' or 'direct'")
+        self.arenas = optimizer.arenas
+        self.device = self.arenas[0].device
+        self.side = torch.cuda.Stream(device=self.device)
+        self._full: Optional[Image] = None
+        self._shard: Optional[Image] = None
+        self._shard_key = None
+        self._writer: Optional[threading.Thread] = None
+        self._writer_error: Optional[BaseException] = None
+        self.last_stats: Dict[str, Any] = {}
+        # ---- full image layout: one record per dtype; arenas first (p | m | v), extras after ----
+        by_dtype: "OrderedDict[torch.dtype, List[torch.Tensor]]" = OrderedDict()
+        for a in self.arenas:
+            by_dtype.setdefault(a.dtype, []).extend([a.p, a.m, a.v])
+        self._arena_ranges = [(t.data_ptr(), t.data_ptr() + t.numel() * t.element_size())
+                              for a in self.arenas for t in (a.p, a.m, a.v)]
+        self.extras: List[torch.Tensor] = []
+        for _, t in self.module.state_dict().items():
+            if t.is_cuda and not self._in_arena(t):
+                t = t if t.is_contiguous() else t.contiguous()
+                by_dtype.setdefault(t.dtype, []).append(t)
+                self.extras.append(t)
+        self.records: "OrderedDict[str, dict]" = OrderedDict()
+        self.full_pieces: List[Piece] = []
+        img_off = 0
+        for ri, (dtype, tensors) in enumerate(by_dtype.items()):
+            key, rec_off, start = str(ri), 0, img_off
+            for t in tensors:
+                self.full_pieces.append(Piece(t, start + rec_off, key, rec_off, start + rec_off))
+                rec_off += _round_up(t.numel() * t.element_size(), ALIGN)
+            self.records[key] = {"dtype": dtype, "off": start, "nbytes": rec_off}
+            img_off = start + rec_off
+        self.full_bytes = max(img_off, ALIGN)
+
+    # ------------------------------------------------------------------ layout helpers ----
+    def _in_arena(self, t: torch.Tensor) -> bool:
+        p = t.data_ptr()
+        return any(lo <= p < hi for lo, hi in self._arena_ranges)
+
+    def full(self) -> Image:
+        if self._full is None:
+            self._full = Image(self.full_pieces, self.full_bytes, self.device, self.mode == "staged")
+        return self._full
+
+    def shard_pieces(self, rank: int, world: int) -> List[Tuple[int, int]]:
+        """(global image offset, nbytes) runs that rank `rank` of `world` owns: its element slice
+        of every arena tensor (16-byte granular, the reduce-scatter slice of K1); rank 0 also owns
+        the stray tensors."""
+        runs = []
+        for p in self.full_pieces:
+            if self._in_arena(p.tensor):
+                nvec = (p.nbytes + 15) // 16
+                per = (nvec + world - 1) // world
+                lo, hi = min(per * rank, nvec) * 16, min(per * (rank + 1), nvec) * 16
+                hi = min(hi, p.nbytes)
+                if hi > lo:
+                    runs.append((p.global_off + lo, hi - lo))
+            elif rank == 0 and p.nbytes:
+                runs.append((p.global_off, p.nbytes))
+        return runs
+
+    def shard(self, rank: int, world: int) -> Image:
+        if self._shard is None or self._shard_key != (rank, world):
+            if self._shard is not None:
+                self._shard.close()
+            pieces, off = [], 0
+            for p in self.full_pieces:
+                flat = p.tensor.reshape(-1).view(torch.uint8)
+                for goff, n in self.shard_pieces(rank, world):
+                    if p.global_off <= goff < p.global_off + max(p.nbytes, 1):
+                        lo = goff - p.global_off
+                        pieces.append(Piece(flat[lo:lo + n], off, global_off=goff))
+                        off += _round_up(n, ALIGN)
+            self._shard = Image(pieces, off, self.device, self.mode == "staged")
+            self._shard_key = (rank, world)
+        return self._shard
+
+    def _locate(self, t: torch.Tensor) -> Optional[Tuple[str, int]]:
+        p = t.data_ptr()
+        for s in self.full_pieces:
+            base = s.tensor.data_ptr()
+            if base <= p < base + max(s.nbytes, 1) and t.dtype == s.tensor.dtype:
+                return s.record, (s.rec_off + (p - base)) // t.element_size()
+        return None
+
+    def stubify(self, obj: Any, small: Dict[torch.dtype, list]) -> Any:
+        """Replace every tensor of a nested state by a TensorStub.  CUDA tensors inside a piece
+        point into the big records; anything else lands in a small per-dtype host record (step
+        scalars, RNG state, ...)."""
+        if isinstance(obj, torch.Tensor):
+            loc = self._locate(obj) if obj.is_cuda and obj.is_contiguous() else None
+            if loc is not None:
+                rec = PT.RecordRef(loc[0], obj.dtype, self.records[loc[0]]["nbytes"] // obj.element_size())
+                return PT.TensorStub(rec, loc[1], obj.shape)
+            host = obj.detach().to("cpu").contiguous()
+            bucket = small.setdefault(host.dtype, [])
+            off = sum(t.numel() for t in bucket)
+            bucket.append(host.reshape(-1).clone())
+            return _Small(host.dtype, off, tuple(host.shape))
+        if isinstance(obj, dict):
+            return type(obj)((k, self.stubify(v, small)) for k, v in obj.items())
+        if isinstance(obj, list):
+            return [self.stubify(v, small) for v in obj]
+        if isinstance(obj, tuple):
+            return tuple(self.stubify(v, small) for v in obj)
+        return copy.deepcopy(obj)
+
+    # ------------------------------------------------------------------ writer plumbing ---
+    def wait(self) -> None:
+        """Join the writer of the previous save (durability point); re-raise its failure."""
+        if self._writer is not None:
+            self._writer.join()
+            self._writer = None
+        if self._writer_error is not None:
+            err, self._writer_error = self._writer_error, None
+            raise RuntimeError(f"checkpoint writer failed: {err!r}") from err
+
+    def _spawn(self, work) -> None:
+        def run():
+            try:
+                work()
+            except BaseException as e:       # surfaced by wait()
+                self._writer_error = e
+        self._writer = threading.Thread(target=run, name="pyrecover-b200-writer")
+        self._writer.start()
+
+    def _fence_optimizer(self, e: torch.cuda.Event) -> None:
+        if self.mode == "direct":            # live arenas must not change before they were read
+            self.optimizer._snapshot_fence = e
+
+    # ------------------------------------------------------------------ vanilla (.pt) -----
+    def save_vanilla(self, path: str, state: Dict[str, Any], verify: bool, max_keep: int,
+                     blocking: bool = False) -> None:
+        """`state` is the reference's dict (epoch, step, model, optimizer, lr_scheduler, ...) with
+        live tensors; python leaves are copied now, tensor bytes are captured by the pack."""
+        t0 = time.perf_counter()
+        self.wait()                          # the pinned arena is about to be overwritten
+        img = self.full()
+        e_copied = img.stage(self.side)
+        self._fence_optimizer(e_copied)
+        small: Dict[torch.dtype, list] = {}
+        frozen = self.stubify(state, small)
+        small_bufs = {dt: torch.cat(parts) for dt, parts in small.items()}
+        path = str(path)
+        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
+
+        def work():
+            t1 = time.perf_counter()
+            e_copied.synchronize()
+            t2 = time.perf_counter()
+            records = [(key, img.host.view(r["off"], r["nbytes"])) for key, r in self.records.items()]
+            refs = {}
+            for i, (dt, buf) in enumerate(small_bufs.items()):
+                key = f"s{i}"
+                refs[dt] = PT.RecordRef(key, dt, buf.numel())
+                records.append((key, buf.numpy().view("uint8").data if buf.numel() else b""))
+            final = _finish_small(frozen, refs)
+            A, B = img.checksum()
+            final["b200"] = {"format": 1, "sum64": [A, B], "image_bytes": img.image_bytes,
+                             "records": {k: [str(r["dtype"]), r["off"], r["nbytes"]] for k, r in self.records.items()}}
+            info = PT.write_archive(path, PT.dumps_state(final), records, md5=verify)
+            if verify:
+                with open(path + ".md5", "w") as f:      # reference side-car, checkpoint.py:81-83
+                    f.write(info["md5"])
+            with open(path + ".b200sum", "w") as f:
+                json.dump({"sum64": [A, B], "image_bytes": img.image_bytes, "file_bytes": info["bytes"],
+                           "record_offsets": info["offsets"]}, f)
+            rotate_files(Path(path).parent, max_keep)
+            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=info["bytes"])
+
+        self._spawn(work)
+        if blocking:
+            self.wait()
+
+    def load_vanilla_image(self, path: str, meta: Dict[str, Any], verify: bool) -> None:
+        """Fast restore of a file written by save_vanilla: the records are contiguous in the file
+        in image order, so the whole image is read with large reads into the pinned arena."""
+        self.wait()
+        img = self.full()
+        if int(meta["image_bytes"]) != img.image_bytes:
+            raise RuntimeError("checkpoint image layout differs from the live model")
+        offs = PT.record_offsets(path)
+        mv = img.host.view()
+        with open(path, "rb", buffering=0) as f:
+            for key, r in self.records.items():
+                off, size = offs[f"data/{key}"]
+                if size != r["nbytes"]:
+                    raise RuntimeError(f"record {key}: {size} bytes on disk, {r['nbytes']} expected")
+                f.seek(off)
+                _read_exact(f, mv[r["off"]:r["off"] + size], path)
+        got = img.restore()
+        if verify and tuple(meta["sum64"]) != got:
+            raise RuntimeError(f"Checksum mismatch for checkpoint {path}: stored {tuple(meta['sum64'])}, "
+                               f"computed on GPU {got}")
+
+    # ------------------------------------------------------------------ sharded directory -
+    def save_sharded(self, dirpath: str, small_state: Dict[str, Any], rank: int, world: int,
+                     max_keep: int, blocking: bool = False) -> None:
+        """Every rank writes `shard_<rank>.bin` (its slice of p, m, v) + `shard_<rank>.json`;
+        rank 0 also writes `meta.pt` (python-side state) and rotates old directories.  The
+        directory is complete when `COMPLETE_<rank>` exists for every rank."""
+        t0 = time.perf_counter()
+        self.wait()
+        img = self.shard(rank, world)
+        e_copied = img.stage(self.side)
+        self._fence_optimizer(e_copied)
+        small_state = _to_cpu(small_state)
+        d = Path(dirpath)
+        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
+
+        def work():
+            t1 = time.perf_counter()
+            d.mkdir(parents=True, exist_ok=True)
+            e_copied.synchronize()
+            t2 = time.perf_counter()
+            K.file_write_atomic(str(d / f"shard_{rank:05d}.bin"), [(img.host.ptr, img.image_bytes)])
+            A, B = img.checksum()
+            side = {"format": SHARD_FORMAT, "rank": rank, "world": world, "sum64": [A, B],
+                    "image_bytes": img.image_bytes, "full_image_bytes": self.full_bytes,
+                    "pieces": [[p.global_off, p.nbytes, p.img_off] for p in img.pieces]}
+            _write_text_atomic(d / f"shard_{rank:05d}.json", json.dumps(side))
+            if rank == 0:
+                torch.save(small_state, str(d / "meta.pt.tmp"))
+                os.replace(str(d / "meta.pt.tmp"), str(d / "meta.pt"))
+            else:
+                torch.save({"rng_state": small_state.get("rng_state")}, str(d / f"rng_{rank:05d}.pt"))
+            _write_text_atomic(d / f"COMPLETE_{rank:05d}", str(world))
+            if rank == 0:
+                rotate_dirs(d.parent, max_keep)
+            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=img.image_bytes)
+
+        self._spawn(work)
+        if blocking:
+            self.wait()
+
+    def load_sharded(self, dirpath: str, verify: bool = True) -> Dict[str, Any]:
+        """Read every shard of the directory (any saving world size) into the full pinned image,
+        upload, unpack into the live tensors, and verify each shard's PR-SUM64 on the GPU plus
+        that the shard sums add up to the image's.  Returns meta.pt's dict."""
+        self.wait()
+        d = Path(dirpath)
+        sides = sorted(d.glob("shard_*.json"))
+        if not sides:
+            raise RuntimeError(f"No checkpoint shards found in {d}")
+        infos = [json.loads(s.read_text()) for s in sides]
+        world = infos[0]["world"]
+        if len(infos) != world or any(not (d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos):
+            raise RuntimeError(f"Sharded checkpoint {d} is incomplete ({len(infos)} of {world} shards)")
+        if infos[0]["full_image_bytes"] != self.full_bytes:
+            raise RuntimeError("checkpoint image layout differs from the live model")
+        img = self.full()
+        mv = img.host.view()
+        for info in infos:
+            with open(d / f"shard_{info['rank']:05d}.bin", "rb", buffering=0) as f:
+                for goff, n, loff in info["pieces"]:
+                    f.seek(loff)
+                    _read_exact(f, mv[goff:goff + n], str(d))
+        img.restore()
+        if verify:
+            image = img._last_image
+            for info in infos:
+                s = torch.zeros(2, dtype=torch.int64, device=self.device)
+                for goff, n, loff in info["pieces"]:
+                    K.checksum_into(image[goff:goff + n], s, loff // 4)
+                if K._sum_to_ints(s) != tuple(info["sum64"]):
+                    raise RuntimeError(f"Checksum mismatch for shard {info['rank']} of {d}")
+        return torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
+
+    def close(self) -> None:
+        self.wait()
+        torch.cuda.synchronize(self.device)
+        for im in (self._full, self._shard):
+            if im is not None:
+                im.close()
+        self._full = self._shard = None
+
+
+# ---------------------------------------------------------------------- small helpers -----
+class _Small:
+    __slots__ = ("dtype", "off", "shape")
+
+    def __init__(self, dtype, off, shape):
+        self.dtype, self.off, self.shape = dtype, off, shape
+
+
+def _finish_small(obj: Any, refs: Dict[torch.dtype, PT.RecordRef]) -> Any:
+    if isinstance(obj, _Small):
+        return PT.TensorStub(refs[obj.dtype], obj.off, obj.shape)
+    if isinstance(obj, dict):
+        return type(obj)((k, _finish_small(v, refs)) for k, v in obj.items())
+    if isinstance(obj, list):
+        return [_finish_small(v, refs) for v in obj]
+    if isinstance(obj, tuple):
+        return tuple(_finish_small(v, refs) for v in obj)
+    return obj
+
+
+def _to_cpu(obj: Any) -> Any:
+    if isinstance(obj, torch.Tensor):
+        return obj.detach().to("cpu").clone()
+    if isinstance(obj, dict):
+        return type(obj)((k, _to_cpu(v)) for k, v in obj.items())
+    if isinstance(obj, list):
+        return [_to_cpu(v) for v in obj]
+    if isinstance(obj, tuple):
+        return tuple(_to_cpu(v) for v in obj)
+    return copy.deepcopy(obj)
+
+
+def _read_exact(f, mv: memoryview, what: str) -> None:
+    got, n = 0, mv.nbytes
+    while got < n:
+        k = f.readinto(mv[got:got + COPY_CHUNK])
+        if not k:
+            raise RuntimeError(f"{what}: truncated checkpoint ({got} of {n} bytes)")
+        got += k
+
+
+def _write_text_atomic(path: Path, text: str) -> None:
+    tmp = str(path) + ".tmp"
+    with open(tmp, "w") as f:
+        f.write(text)
+    os.replace(tmp, str(path))
+
+
+# ---------------------------------------------------------------------- rotation ----------
+_STEP_RE = re.compile(r"ckpt_(\d+)")
+
+
+def _step_key(p: Path):
+    m = _STEP_RE.search(p.name)
+    return (int(m.group(1)) if m else -1, "_final" in p.name, p.name)
+
+
+def rotate_files(base: Path, max_keep: int) -> None:
+    """Keep the newest `max_keep` vanilla checkpoints (reference pyrecover/checkpoint.py:87-101),
+    ordered by STEP NUMBER rather than lexicographically (ckpt_1000.pt sorts after ckpt_200.pt)."""
+    if max_keep <= 0:
+        return
+    files = sorted((x for x in base.glob("**/*.pt") if x.is_file()), key=_step_key)
+    for f in files[:-max_keep] if len(files) > max_keep else []:
+        for side in ("", ".md5", ".b200sum"):
+            try:
+                os.remove(str(f) + side)
+            except FileNotFoundError:
+                pass
+
+
+def rotate_dirs(base: Path, max_keep: int) -> None:
+    """Same for sharded checkpoint directories; only `ckpt_*` directories are candidates (the
+    reference deletes ANY old directory, pyrecover/checkpoint.py:277-292)."""
+    if max_keep <= 0:
+        return
+    import shutil
+    dirs = sorted((x for x in base.glob("ckpt_*") if x.is_dir()), key=_step_key)
+    for x in dirs[:-max_keep] if len(dirs) > max_keep else []:
+        shutil.rmtree(x, ignore_errors=True)
