@@ -46,6 +46,8 @@ const char *pr_last_error(void);
 int pr_abi_version(void);
 /* SM count / compute capability of the current device. */
 int pr_device_info(int *sm_count, int *cc_major, int *cc_minor);
+/* Number of kernels this library has launched in this process (all entry points). */
+uint64_t pr_launch_count(void);
 
 /* ---------------------------------------------------------------- K2: AdamW ----------
  * Replaces optimizer.step() -- reference train.py:274, constructed at train.py:120-122 as

@@ -251,6 +251,23 @@ def save_ckpt_distributed(
     return checkpoint_path
 
 
+def _materialize_adam_state(optimizer) -> None:
+    """torch creates Adam's moments lazily at the first step (torch/optim/adam.py:168-184) and
+    torch.distributed.checkpoint uses `optimizer.state_dict()` as its load template, so a resume
+    into a FRESH optimizer silently drops exp_avg / exp_avg_sq (reference defect, SURVEY.md
+    section 5).  Give every parameter a zero state first so the template has the keys."""
+    if not isinstance(optimizer, (torch.optim.Adam, torch.optim.AdamW)) or len(optimizer.state) > 0:
+        return
+    for group in optimizer.param_groups:
+        on_device = bool(group.get("fused") or group.get("capturable"))
+        for p in group["params"]:
+            if not p.requires_grad:
+                continue
+            step = torch.zeros((), dtype=torch.float32, device=p.device if on_device else "cpu")
+            optimizer.state[p] = {"step": step, "exp_avg": torch.zeros_like(p, memory_format=torch.preserve_format),
+                                  "exp_avg_sq": torch.zeros_like(p, memory_format=torch.preserve_format)}
+
+
 def _dcp_objects(model, optimizer, lr_scheduler, sampler, epoch, step) -> Dict[str, Any]:
     objs = {"model": model, "optimizer": optimizer, "metadata": {"epoch": epoch, "step": step}}
     if lr_scheduler is not None:
@@ -313,6 +330,7 @@ def load_ckpt_distributed(
         epoch, step = small["epoch"], small["step"]
     else:
         import torch.distributed.checkpoint as dist_cp
+        _materialize_adam_state(optimizer)
         objs = _dcp_objects(model, optimizer, lr_scheduler, sampler, 0, 0)
         dist_cp.load(state_dict=objs, checkpoint_id=checkpoint_path,
                      storage_reader=dist_cp.FileSystemReader(checkpoint_path))

@@ -32,6 +32,7 @@ _SIGNATURES = {
     "pr_last_error": (c_char_p, []),
     "pr_abi_version": (c_int, []),
     "pr_device_info": (c_int, [POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "pr_launch_count": (c_uint64, []),
     "pr_adamw": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_int,
                          POINTER(AdamWArgs), c_void_p]),
     "pr_checksum": (c_int, [c_void_p, c_uint64, c_uint64, c_void_p, c_void_p]),

@@ -155,6 +155,7 @@ extern "C" int pr_adamw(void *p, const void *g, void *m, void *v, uint64_t n, in
                                                                         (uint4 *)v, nvec, c);
         }
         PR_CUDA(cudaGetLastError());
+        pr_count_launch();
     }
     uint64_t done = nvec * per_vec;
     if (done < n) {
@@ -164,6 +165,7 @@ extern "C" int pr_adamw(void *p, const void *g, void *m, void *v, uint64_t n, in
         else
             adamw_scalar_kernel<0><<<grid, 256, 0, stream>>>(p, g, m, v, done, n, dtype, a->grad_dtype, c);
         PR_CUDA(cudaGetLastError());
+        pr_count_launch();
     }
     return PR_OK;
 }

@@ -319,6 +319,7 @@ static int launch(pr_comm *c, const void *kernel, int grid, cudaStream_t stream,
     dim3 g(grid, c->emulated ? c->world : 1, 1), b(kThreads, 1, 1);
     if (c->emulated) PR_CUDA(cudaLaunchCooperativeKernel(kernel, g, b, argv, 0, stream));
     else PR_CUDA(cudaLaunchKernel(kernel, g, b, argv, 0, stream));
+    pr_count_launch();
     return PR_OK;
 }
 

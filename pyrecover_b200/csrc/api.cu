@@ -1,9 +1,14 @@
 // Error plumbing and device queries of libpyrecover_b200 (C ABI: include/pyrecover_b200.h).
 #include <stdarg.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 static thread_local char g_err[1024] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void pr_count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
 void pr_set_error(const char *fmt, ...) {
     va_list ap;
@@ -40,3 +45,5 @@ extern "C" int pr_device_info(int *sm_count, int *cc_major, int *cc_minor) {
     if (cc_minor) *cc_minor = minor;
     return PR_OK;
 }
+
+extern "C" uint64_t pr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }

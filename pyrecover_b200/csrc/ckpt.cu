@@ -224,6 +224,7 @@ extern "C" int pr_checksum(const void *data, uint64_t nbytes, uint64_t word_base
         checksum_unaligned_kernel<<<grid, kThreads, 0, stream>>>((const uint8_t *)data, nbytes,
                                                                  word_base, sum);
     PR_CUDA(cudaGetLastError());
+    pr_count_launch();
     return PR_OK;
 }
 
@@ -325,6 +326,7 @@ static int launch_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, voi
     else
         pack_kernel<UNPACK, false><<<grid, kThreads, 0, stream>>>(plan->dev, (uint8_t *)image, nullptr);
     PR_CUDA(cudaGetLastError());
+    pr_count_launch();
     return PR_OK;
 }
 

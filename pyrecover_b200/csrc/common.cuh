@@ -29,6 +29,7 @@ void pr_set_error(const char *fmt, ...);   // api.cu
     } while (0)
 
 int pr_sm_count();   // api.cu: SM count of the current device (cached per device)
+void pr_count_launch(int n = 1);   // api.cu: bumps the counter pr_launch_count() reports
 
 static inline bool pr_aligned16(const void *p) { return (((uintptr_t)p) & 15u) == 0; }
 

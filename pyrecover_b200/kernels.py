@@ -30,6 +30,11 @@ def device_info():
     return sm.value, major.value, minor.value
 
 
+def launch_count() -> int:
+    """Kernels launched by libpyrecover_b200 in this process so far."""
+    return int(lib().pr_launch_count())
+
+
 # ------------------------------------------------------------------------- K2 AdamW -----
 
 def adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, numerics=0,

@@ -115,8 +115,15 @@ class B200AdamW(torch.optim.Optimizer):
             arena.gather_grads()
             self._steps[gi] += 1
             self._step_tensors[gi].fill_(self._steps[gi])
+            events = getattr(self, "kernel_events", None)      # bench.py: CUDA events around K2
+            if events is not None:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
                      weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group))
+            if events is not None:
+                e1.record()
+                events.append((e0, e1))
         return loss
 
     # ------------------------------------------------------------------ state dict -------

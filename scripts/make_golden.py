@@ -154,7 +154,7 @@ def gen_checksum_kat():
     print("wrote checksum_kat")
 
 
-if __name__ == "__main__":
+def main():
     OUT.mkdir(parents=True, exist_ok=True)
     gen_adamw(torch.bfloat16, "adamw_bf16.npz")
     gen_adamw(torch.float32, "adamw_f32.npz")
@@ -162,3 +162,34 @@ if __name__ == "__main__":
     gen_ddp(4)
     gen_ref_ckpt()
     gen_checksum_kat()
+    gen_boundary()
+
+
+def gen_boundary():
+    """Dump the reference's CLI defaults and checkpoint-function signatures (the boundary)."""
+    import inspect
+    import json
+    sys.path.insert(0, str(REF))
+    old = sys.argv
+    sys.argv = ["train.py"]
+    try:
+        ref_utils = sys.modules.get("ref_utils") or _load(REF / "utils.py", "ref_utils")
+        flags = vars(ref_utils.get_args())
+    finally:
+        sys.argv = old
+    (OUT / "reference_flags.json").write_text(json.dumps(flags, indent=1, sort_keys=True))
+    ck = _load(REF / "pyrecover" / "checkpoint.py", "ref_checkpoint2")
+    sigs = {}
+    for name in ("save_ckpt_vanilla", "load_ckpt_vanilla", "save_ckpt_distributed", "load_ckpt_distributed",
+                 "get_latest_checkpoint"):
+        sig = inspect.signature(getattr(ck, name))
+        sigs[name] = [[p.name, None if p.default is inspect._empty else p.default] for p in sig.parameters.values()]
+    (OUT / "reference_signatures.json").write_text(json.dumps(sigs, indent=1))
+    print("wrote boundary fixtures")
+
+
+if __name__ == "__main__":
+    if "--boundary-only" in sys.argv:
+        gen_boundary()
+    else:
+        main()

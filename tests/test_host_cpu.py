@@ -1,0 +1,305 @@
+"""CPU tests (no GPU): the C-ABI library loads and exports every declared symbol, the boundary
+(flags, pyrecover API), host logic (time-aware policy, rotation, archive writer, layouts) and
+BASELINE config 1 (tiny model, DDP on gloo, world 2, checkpoint every 10 steps, resume equality)."""
+import hashlib
+import inspect
+import json
+import os
+import re
+import subprocess
+import sys
+import time
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+# ------------------------------------------------------------------------- C ABI ----------
+def _declared_symbols():
+    text = (ROOT / "include" / "pyrecover_b200.h").read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(pr_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_builds_loads_and_exports_every_declared_symbol():
+    from pyrecover_b200 import _lib
+    _lib.build()
+    L = _lib.lib()
+    declared = _declared_symbols()
+    assert len(declared) >= 25
+    for name in declared:
+        assert hasattr(L, name), f"{name} declared in include/pyrecover_b200.h but not exported"
+    assert sorted(_lib.EXPORTED_SYMBOLS) == declared, "ctypes table and header disagree"
+    assert L.pr_abi_version() == 1
+    assert L.pr_last_error() is not None
+
+
+def test_product_never_imports_the_oracle():
+    """The oracle is test infrastructure: nothing under pyrecover_b200/ or pyrecover/ (nor the
+    train.py boundary) may import or open it."""
+    for base in ("pyrecover_b200", "pyrecover"):
+        for f in (ROOT / base).rglob("*.py"):
+            assert "oracle" not in f.read_text(), f
+    for f in ("train.py", "utils.py", "dist_utils.py"):
+        assert "oracle" not in (ROOT / f).read_text(), f
+
+
+def test_kernels_refuse_cpu_tensors():
+    from pyrecover_b200 import kernels as K
+    t = torch.zeros(16, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        K.adamw_(t, t, t, t, lr=1e-3)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        K.checksum(t)
+    from pyrecover_b200.optim import B200AdamW
+    with pytest.raises(RuntimeError, match="CUDA"):
+        B200AdamW([torch.nn.Parameter(torch.zeros(4))], lr=1e-3)
+
+
+# ------------------------------------------------------------------------- boundary -------
+def test_reference_flags_names_types_defaults():
+    """tests/golden/reference_flags.json was dumped from the reference's own get_args()
+    (utils.py:105-261) by scripts/make_golden.py."""
+    import utils
+    ref = json.loads((ROOT / "tests" / "golden" / "reference_flags.json").read_text())
+    ours = vars(utils.get_args([]))
+    assert len(ref) == 28
+    for k, v in ref.items():
+        assert k in ours, k
+        assert ours[k] == v, (k, ours[k], v)
+    a = utils.get_args(["--use-torch-distributed-ckpt", "--timeaware-checkpointing", "--experiment_name=x",
+                        "--sequence-length=128", "--resume-from-checkpoint", "latest", "--fused-optimizer"])
+    assert a.use_torch_distributed_ckpt and a.timeaware_checkpointing and a.sequence_length == 128
+
+
+def test_pyrecover_api_signatures_match_reference():
+    """Positional order matters: the reference's train.py passes 4 (load) / 7 (save) positionally."""
+    import pyrecover
+    from pyrecover import checkpoint as ck
+    ref = json.loads((ROOT / "tests" / "golden" / "reference_signatures.json").read_text())
+    for name, params in ref.items():
+        sig = inspect.signature(getattr(ck, name))
+        got = [[p.name, None if p.default is inspect._empty else p.default] for p in sig.parameters.values()]
+        assert got == params, name
+    assert callable(pyrecover.setup_resubmission) and callable(pyrecover.get_remaining_time)
+
+
+def test_lr_schedule_matches_reference_formula():
+    import utils
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.AdamW([p], lr=1e-5)
+    sched = utils.build_lr_scheduler(opt, 10)
+    lrs = []
+    for _ in range(13):
+        lrs.append(opt.param_groups[0]["lr"])
+        opt.step()
+        sched.step()
+    ref = np.load(ROOT / "tests" / "golden" / "adamw_bf16.npz")["lrs"]
+    assert np.array_equal(np.array(lrs[:12]), ref)
+    assert lrs[12] == 1e-5
+    assert sched.state_dict()["lr_lambdas"] == [{"warmup_steps": 10}]
+
+
+# ------------------------------------------------------------------------- time-aware -----
+def test_time_aware_policy_thresholds():
+    from pyrecover.timelimit import TimeAwarePolicy, get_remaining_time
+    now = [1000.0]
+    pol = TimeAwarePolicy(1.0, 10.0, end_time=1100.0, clock=lambda: now[0])
+    assert pol.buffer_time == 10 * 1.0 + 2 * 10.0            # train.py:166-176
+    assert pol.threshold == 1.0 + 10.0 + 30.0
+    assert not pol.should_stop()
+    now[0] = 1059.5
+    assert pol.should_stop()                                 # 40.5 left < 41 (train.py:226-228)
+    assert pol.observe_iteration(2.0) and pol.max_iter_time == 2.0
+    assert pol.buffer_time == 5 * 2.0 + 1 * 10.0             # train.py:303
+    assert not pol.observe_iteration(1.5)
+    assert pol.observe_checkpoint(12.0) and pol.max_ckpt_time == 12.0
+    assert TimeAwarePolicy(1.0, 10.0, end_time=None).should_stop() is False
+    os.environ["SLURM_JOB_END_TIME"] = str(time.time() + 50)
+    try:
+        assert 49 < get_remaining_time() <= 50
+        os.environ["SLURM_JOB_END_TIME"] = "garbage"
+        assert get_remaining_time() is None
+    finally:
+        del os.environ["SLURM_JOB_END_TIME"]
+
+
+def test_resubmission_handler_sets_flag():
+    import signal
+
+    from pyrecover.resubmit import setup_resubmission
+    old = signal.getsignal(signal.SIGUSR1)
+    try:
+        seen = []
+        st = setup_resubmission(None, signals=(signal.SIGUSR1,), on_signal=seen.append)
+        os.kill(os.getpid(), signal.SIGUSR1)
+        time.sleep(0.05)
+        assert st.stop_requested and seen == [signal.SIGUSR1] and not st.resubmitted
+    finally:
+        signal.signal(signal.SIGUSR1, old)
+
+
+# ------------------------------------------------------------------------- rotation -------
+def test_rotation_is_by_step_number_and_scoped(tmp_path):
+    from pyrecover_b200.snapshot import rotate_dirs, rotate_files
+    for s in (90, 100, 200, 1000):
+        (tmp_path / f"ckpt_{s}.pt").write_bytes(b"x")
+        (tmp_path / f"ckpt_{s}.pt.md5").write_text("m")
+    rotate_files(tmp_path, 2)
+    assert sorted(p.name for p in tmp_path.glob("*.pt")) == ["ckpt_1000.pt", "ckpt_200.pt"]   # lexicographic would keep 90 & 200
+    assert not (tmp_path / "ckpt_90.pt.md5").exists()
+    rotate_files(tmp_path, 0)
+    assert len(list(tmp_path.glob("*.pt"))) == 2
+    for s in (5, 10, 15):
+        (tmp_path / f"ckpt_{s}").mkdir()
+    (tmp_path / "logs").mkdir()
+    rotate_dirs(tmp_path, 1)
+    assert (tmp_path / "logs").exists() and (tmp_path / "ckpt_15").exists() and not (tmp_path / "ckpt_5").exists()
+
+
+# ------------------------------------------------------------------------- archive --------
+def test_archive_writer_is_torch_loadable_and_aligned(tmp_path):
+    from collections import OrderedDict
+
+    from pyrecover_b200 import ptfile as PT
+    n = 1000
+    p, m = torch.randn(n).bfloat16(), torch.randn(n).bfloat16()
+    image = torch.cat([p, m]).view(torch.uint8).numpy().tobytes()
+    rec = PT.RecordRef("0", torch.bfloat16, 2 * n)
+    srec = PT.RecordRef("s0", torch.float32, 1)
+    state = {"epoch": 1, "step": 7,
+             "model": OrderedDict(w=PT.TensorStub(rec, 0, (10, 50)), b=PT.TensorStub(rec, 500, (500,))),
+             "optimizer": {"state": {0: {"step": PT.TensorStub(srec, 0, ()), "exp_avg": PT.TensorStub(rec, n, (10, 50))}},
+                           "param_groups": [{"lr": 1e-5, "betas": (0.9, 0.999), "params": [0]}]}}
+    path = tmp_path / "ckpt_7.pt"
+    info = PT.write_archive(str(path), PT.dumps_state(state), [("0", image), ("s0", np.float32([7.0]).tobytes())], md5=True)
+    assert info["md5"] == hashlib.md5(path.read_bytes()).hexdigest()
+    assert all(o % 64 == 0 for o in info["offsets"].values())
+    assert not Path(str(path) + ".tmp").exists()
+    for kw in ({}, {"mmap": True}, {"weights_only": True}):
+        ck = torch.load(path, map_location="cpu", **kw)
+        assert torch.equal(ck["model"]["w"], p[:500].view(10, 50)) and torch.equal(ck["model"]["b"], p[500:])
+        assert torch.equal(ck["optimizer"]["state"][0]["exp_avg"], m[:500].view(10, 50))
+        assert float(ck["optimizer"]["state"][0]["step"]) == 7.0 and ck["step"] == 7
+    offs = PT.record_offsets(str(path))
+    assert offs["data/0"] == (info["offsets"]["0"], len(image))
+    import zipfile
+    assert zipfile.ZipFile(path).testzip() is None
+
+
+def test_flat_layout_alignment_and_slices():
+    from pyrecover_b200.flat import FlatLayout
+    shapes = [torch.Size(s) for s in [(1024, 256), (128, 256), (256,), (7, 3)]]
+    lay = FlatLayout(shapes, torch.bfloat16, multiple_of=8)
+    assert all(s.offset * 2 % 256 == 0 for s in lay.slots)
+    assert lay.numel % (128 * 8) == 0 and lay.payload == 1024 * 256 + 128 * 256 + 256 + 21
+    flat = torch.arange(lay.numel, dtype=torch.float32).bfloat16()
+    views = lay.views(flat)
+    assert [tuple(v.shape) for v in views] == [tuple(s) for s in shapes]
+    assert views[2].data_ptr() == flat.data_ptr() + lay.slots[2].offset * 2
+
+
+# ------------------------------------------------------------------------- host path ------
+def _small_model(seed):
+    torch.manual_seed(seed)
+    return torch.nn.Sequential(torch.nn.Linear(24, 16, bias=False), torch.nn.Linear(16, 8)).to(torch.bfloat16)
+
+
+def test_host_path_checkpoint_roundtrip_and_reference_fixture(tmp_path, golden_dir):
+    """CPU models take the reference's own route (torch.save / torch.load): round trip is
+    bit-exact, the .md5 side-car verifies, a reference-written file loads, latest-lookup works."""
+    import shutil
+
+    import pyrecover
+    import utils
+    model = _small_model(0)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-5, fused=False)
+    sched = utils.build_lr_scheduler(opt, 10)
+    for _ in range(3):
+        opt.zero_grad()
+        model(torch.randn(4, 24).bfloat16()).float().pow(2).sum().backward()
+        opt.step()
+        sched.step()
+    exp = tmp_path / "exp"
+    exp.mkdir()
+    for step in (1, 2, 3, 4):
+        pyrecover.save_ckpt_vanilla(model, opt, sched, None, step, 1, exp / f"ckpt_{step}.pt", max_keep=3, verify=True)
+    assert sorted(p.name for p in exp.glob("*.pt")) == ["ckpt_2.pt", "ckpt_3.pt", "ckpt_4.pt"]
+    assert pyrecover.get_latest_checkpoint(exp) == str(exp / "ckpt_4.pt")
+    m2 = _small_model(1)
+    o2 = torch.optim.AdamW(m2.parameters(), lr=1e-5, fused=False)
+    s2 = utils.build_lr_scheduler(o2, 10)
+    assert pyrecover.load_ckpt_vanilla(m2, o2, s2, None, "latest", experiment_dir=exp, verify=True) == (1, 4)
+    for a, b in zip(model.parameters(), m2.parameters()):
+        assert torch.equal(a, b)
+        assert torch.equal(opt.state[a]["exp_avg_sq"], o2.state[b]["exp_avg_sq"])
+    assert s2.state_dict() == sched.state_dict()
+    # reference-written fixture
+    for f in ("ref_vanilla.pt", "ref_vanilla.pt.md5"):
+        shutil.copy(golden_dir / f, tmp_path / f)
+    assert pyrecover.load_ckpt_vanilla(m2, o2, s2, None, str(tmp_path / "ref_vanilla.pt"), verify=True) == (1, 3)
+    with pytest.raises(RuntimeError, match="No checkpoint found"):
+        pyrecover.load_ckpt_vanilla(m2, o2, s2, None, "latest", experiment_dir=tmp_path / "nothing")
+    (exp / "ckpt_4.pt.md5").write_text("deadbeef")
+    with pytest.raises(RuntimeError, match="Checksum mismatch"):
+        pyrecover.load_ckpt_vanilla(m2, o2, s2, None, str(exp / "ckpt_4.pt"), verify=True)
+
+
+def test_check_weights_equality_criterion_on_our_files(tmp_path):
+    """What the reference's tests/check_weights_equality.py does in vanilla mode (:112-115,
+    :166-178): bare torch.load(path)["model"], max |a-b| <= tolerance per tensor."""
+    import pyrecover
+    model = _small_model(3)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-5)
+    a, b = tmp_path / "a" / "ckpt_1.pt", tmp_path / "b" / "ckpt_1.pt"
+    a.parent.mkdir()
+    b.parent.mkdir()
+    pyrecover.save_ckpt_vanilla(model, opt, None, None, 1, 1, a, verify=False)
+    pyrecover.save_ckpt_vanilla(model, opt, None, None, 1, 1, b, verify=False)
+    A, B = torch.load(a)["model"], torch.load(b)["model"]
+    assert A.keys() == B.keys()
+    assert all(float((A[k].float() - B[k].float()).abs().max()) <= 1e-7 for k in A)
+
+
+# ------------------------------------------------------------------------- config 1 -------
+def _launch(tmp, name, steps, extra=(), nproc=2):
+    env = dict(os.environ, OMP_NUM_THREADS="2", MASTER_ADDR="127.0.0.1")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(29700 + (os.getpid() % 200)),
+           str(ROOT / "train.py"), "--distributed", "--device", "cpu", "--synthetic-data", "--model-preset", "tiny",
+           "--sequence-length", "64", "--batch-size", str(nproc), "--training-steps", str(steps), "--checkpoint-frequency", "10",
+           "--checkpoint-dir", str(tmp), "--experiment_name", name, "--verify-checkpoints", "--logging-frequency", "10",
+           "--learning-rate", "1e-3", *extra]
+    r = subprocess.run(cmd, cwd=str(ROOT), env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r
+
+
+@pytest.mark.parametrize("sharded", [False, True])
+def test_config1_gloo_world2_resume_weight_equality(tmp_path, sharded):
+    """BASELINE.json config 1: tiny transformer, DDP on CPU/gloo world_size 2, synthetic tokens,
+    checkpoint every 10 steps + resume: the interrupted+resumed run ends with exactly the weights
+    of the straight run (tolerance 0)."""
+    extra = ("--use-torch-distributed-ckpt",) if sharded else ()
+    _launch(tmp_path, "straight", 30, extra)
+    _launch(tmp_path, "resumed", 20, extra)
+    out = _launch(tmp_path, "resumed", 30, extra + ("--resume-from-checkpoint", "latest"))
+    assert "step 20" in out.stdout
+    if sharded:
+        import torch.distributed.checkpoint as dcp
+        from torch.distributed.checkpoint.format_utils import dcp_to_torch_save
+        for name in ("straight", "resumed"):
+            dcp_to_torch_save(str(tmp_path / name / "ckpt_30"), str(tmp_path / f"{name}.pt"))
+        A = torch.load(tmp_path / "straight.pt", weights_only=False)
+        B = torch.load(tmp_path / "resumed.pt", weights_only=False)
+        A, B = A["model"], B["model"]
+    else:
+        A = torch.load(tmp_path / "straight" / "ckpt_30.pt")["model"]
+        B = torch.load(tmp_path / "resumed" / "ckpt_30.pt")["model"]
+    assert len(A) >= 39 and A.keys() == B.keys()
+    for k in A:
+        assert float((A[k].float() - B[k].float()).abs().max()) == 0.0, k
