@@ -209,13 +209,13 @@ def run_b200(a):
     # ---------------- leg 2: end to end through the public step (host batches) ----------------
     host_batches = [data.batch(1000 + s) for s in range(total)]
     for s in range(a.warmup):
-        float(trainer.step_from_host(*host_batches[s]))
+        float(trainer.step_from_host(*host_batches[s]).detach())
     barrier()
     t0 = time.perf_counter()
     for s in range(a.warmup, total):
         loss = trainer.step_from_host(*host_batches[s])
         maybe_ckpt(s, "e2e")
-        loss_val = float(loss)            # D2H read of the step's result
+        loss_val = float(loss.detach())   # D2H read of the step's result
     barrier()
     e2e_s = time.perf_counter() - t0
     ckpt.wait_for_checkpoints()
@@ -234,8 +234,8 @@ def run_b200(a):
             evs = []
             for i in range(n):
                 a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                torch.cuda.synchronize()
-                w0 = time.perf_counter()
+                torch.cuda.current_stream().synchronize()   # the training stream only: the side
+                w0 = time.perf_counter()                    # stream keeps draining the snapshot
                 a0.record()
                 trainer.step(*dev_small[i % len(dev_small)])
                 if with_save and i == n // 2:
@@ -243,7 +243,7 @@ def run_b200(a):
                                            ckpt_dir / f"stall_r{rank}" / f"ckpt_{900 + i}.pt", max_keep=1,
                                            verify=False, is_distributed=False, rank=0)
                 a1.record()
-                torch.cuda.synchronize()
+                a1.synchronize()
                 evs.append((a0.elapsed_time(a1), (time.perf_counter() - w0) * 1e3))
             return evs
         dev_small = [tuple(t.to(device) for t in data.batch(5000 + s)) for s in range(4)]

@@ -82,7 +82,8 @@ def save_vanilla(model, opt, sched, step: int, path: str, verify: bool) -> float
 
 
 def run(preset: str, full_seq: int, steps: int, warmup: int, fused: bool = True, budget_s_per_step: float = 10.0,
-        sample_seq: Optional[int] = None, ckpt_path: Optional[str] = None, threads: Optional[int] = None) -> Dict:
+        sample_seq: Optional[int] = None, ckpt_path: Optional[str] = None, threads: Optional[int] = None,
+        max_seconds: float = 90.0) -> Dict:
     """Time `steps` CPU training steps on a bounded token sample of the named workload.
 
     The per-step optimizer / checkpoint cost does not depend on the token count, so tokens/s on a
@@ -104,11 +105,12 @@ def run(preset: str, full_seq: int, steps: int, warmup: int, fused: bool = True,
     train_step(model, opt, sched, x, y)
     t16 = time.perf_counter() - t0
     if sample_seq is None:
-        x64, y64 = SyntheticTokens(vocab, 64, 1).batch(0)
+        x64, y64 = SyntheticTokens(vocab, 144, 1).batch(0)
+        train_step(model, opt, sched, x64, y64)          # first touch of the new shape
         t0 = time.perf_counter()
         train_step(model, opt, sched, x64, y64)
         t64 = time.perf_counter() - t0
-        per_tok = max((t64 - t16) / 48.0, 1e-6)
+        per_tok = max((t64 - t16) / 128.0, 1e-6)
         fixed = max(t16 - 16 * per_tok, 0.0)
         sample_seq = int(max(16, min(full_seq, (budget_s_per_step - fixed) / per_tok)))
         sample_seq = max(16, sample_seq // 16 * 16)
@@ -116,9 +118,14 @@ def run(preset: str, full_seq: int, steps: int, warmup: int, fused: bool = True,
     for s in range(warmup):
         train_step(model, opt, sched, *data.batch(s))
     t0 = time.perf_counter()
+    done = 0
     for s in range(steps):
         loss = train_step(model, opt, sched, *data.batch(warmup + s))
-        float(loss)
+        float(loss.detach())
+        done += 1
+        if time.perf_counter() - t0 > max_seconds:      # keep the whole arm within minutes
+            break
+    steps = done
     dt = time.perf_counter() - t0
     out = {"tokens_per_s": sample_seq * steps / dt, "ms_per_step": 1e3 * dt / steps, "cores": cores,
            "sample_seq": sample_seq, "steps": steps, "probe_first_step_s": t_probe,

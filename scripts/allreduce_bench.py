@@ -1,0 +1,166 @@
+#!/usr/bin/env python
+"""Multi-GPU micro-benchmark + parity check of K1 (P2P allreduce) and the fused K1+K2 kernel
+against NCCL (BASELINE.json config 5: bucket sweep at 2/4/8 GPUs vs the reference's DDP/NCCL).
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port 29511 scripts/allreduce_bench.py [--max-log2 30] [--json out.json]
+
+Timing: CUDA events on the launching stream, 5 warm-ups + 20 timed launches, median, MAX over
+ranks.  bus GB/s = N_bytes / t * 2 (W-1) / W (nccl-tests convention); the roofline is the measured
+770 GB/s peer copy (900 GB/s nominal) per direction per GPU.
+Parity: every rank's result must be bit-identical across ranks and equal to the fp32 rank-order
+sum rounded once (computed here with torch in fp32 from all_gathered inputs); NCCL's own result
+is compared within the stated bf16 bound.
+"""
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+from pyrecover_b200 import _lib  # noqa: E402
+from pyrecover_b200 import kernels as K  # noqa: E402
+
+
+def timed(fn, iters=20, warmup=5):
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    t = torch.tensor([ts[len(ts) // 2]], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--min-log2", type=int, default=20)
+    ap.add_argument("--max-log2", type=int, default=30)
+    ap.add_argument("--json", type=str, default=None)
+    ap.add_argument("--max-blocks", type=int, default=0)
+    a = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    maxb = 1 << a.max_log2
+    comm = K.Comm(rank, world)
+    for region in range(4):
+        comm.alloc_region(region, maxb)
+    comm.connect()
+    G = comm.region_tensor(0, torch.bfloat16)
+    P = comm.region_tensor(1, torch.bfloat16)
+    M = comm.region_tensor(2, torch.bfloat16)
+    V = comm.region_tensor(3, torch.bfloat16)
+    results = {"world": world, "rows": []}
+    scale = 1.0 / world
+
+    # ---------------- parity at 8 MiB -----------------------------------------------------------
+    n = (8 << 20) // 2
+    g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+    local_g = (torch.randn(n, generator=g, device=dev) * 1e-3).bfloat16()
+    gathered = [torch.empty_like(local_g) for _ in range(world)]
+    dist.all_gather(gathered, local_g)
+    acc = torch.zeros(n, dtype=torch.float32, device=dev)
+    for t in gathered:                       # rank order 0..W-1, fp32
+        acc = acc + t.float()
+    expect = (acc * scale).bfloat16()
+    for algo, name in ((_lib.PR_AR_TWO_SHOT, "two_shot"), (_lib.PR_AR_ONE_SHOT, "one_shot")):
+        nb = n * 2 if algo == _lib.PR_AR_TWO_SHOT else 1 << 20
+        G[:n].copy_(local_g)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce(0, 0, nb, torch.bfloat16, scale, algo=algo, max_blocks=a.max_blocks)
+        torch.cuda.synchronize()
+        ok = torch.equal(G[:nb // 2], expect[:nb // 2])
+        flag = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        results[f"parity_{name}"] = bool(flag.item())
+        assert flag.item() == 1, f"{name} allreduce differs from the fp32 rank-order sum on some rank"
+        dist.barrier()
+    nccl = local_g.clone()
+    nccl.mul_(scale)
+    dist.all_reduce(nccl)
+    S = torch.stack([t.float().abs() for t in gathered]).sum(0) / world
+    bound = world * 2.0 ** -9 * S + 1e-30
+    within = bool(((nccl.float() - expect.float()).abs() <= bound).all())
+    results["nccl_within_bound"] = within
+    assert within
+    # fused reduce-scatter -> AdamW -> all-gather vs (allreduce -> pr_adamw) on a private copy
+    p0 = (torch.randn(n, generator=torch.Generator(device="cuda").manual_seed(7), device=dev) * 0.02).bfloat16()
+    G[:n].copy_(local_g); P[:n].copy_(p0); M[:n].zero_(); V[:n].zero_()
+    torch.cuda.synchronize()
+    dist.barrier()
+    args = K.adamw_args(1e-4, 0.9, 0.999, 1e-8, 0.01, step=1, grad_scale=scale)
+    comm.allreduce_adamw(0, 1, 2, 3, 0, n, args, max_blocks=a.max_blocks)
+    comm.allgather_slices(2, 0, n * 2)
+    comm.allgather_slices(3, 0, n * 2)
+    torch.cuda.synchronize()
+    pr, mr, vr = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    K.adamw_(pr, acc, mr, vr, lr=1e-4, step=1, grad_scale=scale)     # fp32 rank-order sum as gradient
+    ok = torch.equal(P[:n], pr) and torch.equal(M[:n], mr) and torch.equal(V[:n], vr)
+    flag = torch.tensor([int(ok)], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    results["parity_fused"] = bool(flag.item())
+    assert flag.item() == 1, "fused allreduce+AdamW differs from allreduce -> AdamW"
+    dist.barrier()
+
+    # ---------------- bandwidth sweep -----------------------------------------------------------
+    for lg in range(a.min_log2, a.max_log2 + 1):
+        nbytes = 1 << lg
+        ne = nbytes // 2
+        buf = torch.empty(ne, dtype=torch.bfloat16, device=dev).normal_(0, 1e-3)
+        row = {"bytes": nbytes}
+        t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, max_blocks=a.max_blocks))
+        row["p2p_ms"], row["p2p_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        if nbytes <= (4 << 20):
+            t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, algo=_lib.PR_AR_ONE_SHOT))
+            row["oneshot_ms"] = t
+        t = timed(lambda: dist.all_reduce(buf))
+        row["nccl_ms"], row["nccl_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        step = [0]
+
+        def fused():
+            step[0] += 1
+            comm.allreduce_adamw(0, 1, 2, 3, 0, ne, K.adamw_args(1e-5, 0.9, 0.999, 1e-8, 0.01, step[0], scale),
+                                 max_blocks=a.max_blocks)
+        t = timed(fused)
+        row["fused_ms"], row["fused_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        pl, ml, vl = (torch.zeros(ne, dtype=torch.bfloat16, device=dev) for _ in range(3))
+
+        def unfused():
+            step[0] += 1
+            dist.all_reduce(buf)
+            K.adamw_(pl, buf, ml, vl, lr=1e-5, step=step[0], grad_scale=scale)
+        t = timed(unfused)
+        row["nccl_plus_adamw_ms"] = t
+        results["rows"].append(row)
+        if rank == 0:
+            print(f"{nbytes >> 20:6d} MiB  p2p {row['p2p_ms']:8.3f} ms {row['p2p_busbw']:7.1f} GB/s | "
+                  f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s | fused AR+AdamW {row['fused_ms']:8.3f} ms | "
+                  f"nccl+adamw {row['nccl_plus_adamw_ms']:8.3f} ms", flush=True)
+        del buf, pl, ml, vl
+    assert not comm.timed_out()
+    if rank == 0 and a.json:
+        Path(a.json).parent.mkdir(parents=True, exist_ok=True)
+        Path(a.json).write_text(json.dumps(results, indent=1))
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
