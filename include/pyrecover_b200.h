@@ -107,6 +107,26 @@ int pr_ckpt_pack(const pr_pack_plan *plan, void *image, uint64_t *sum_dev, void 
 int pr_ckpt_unpack(const pr_pack_plan *plan, const void *image, uint64_t *sum_dev,
                    void *stream);
 
+/* pr_ckpt_pack for callers that must not allocate.  (No counterpart in the reference: its
+ * save path allocates freely.)  A checkpoint matters most when it is hardest to take: in the
+ * walltime / preemption handler of a job that has filled HBM, where the cudaMalloc behind
+ * pr_pack_plan_create can fail or stall the device, or in a process whose memory manager forbids
+ * device allocation after start-up.  Here the tile table lives in a fixed 288 KiB array inside the
+ * library (held on every GPU that loads it, until exit) and the call performs no cudaMalloc,
+ * cudaFree or other allocating call; the caller still supplies the tensors, the image and sum_dev.
+ *   Limits: n <= 1024 tensors and at most 65536 tiles of 64 KiB (4 GiB of payload when tensors
+ *   are tile multiples); beyond either the call fails with PR_ERR_INVALID and says so.
+ *   First call on a device resolves the array's device address (that device must be current);
+ *   make that first call before any stream capture begins.
+ *   All calls share the one array and it keeps the previous call's table; each call rewrites every
+ *   entry it reads, so nothing needs clearing -- but two calls whose GPU work overlaps (different
+ *   streams, or threads racing on one device) would overwrite each other's table: serialise them.
+ * Same results as pr_pack_plan_create + pr_ckpt_pack: image bytes and PR-SUM64 added into sum_dev
+ * (zeroed by the caller; NULL skips the checksum). */
+int pr_ckpt_pack_noalloc(const void *const *tensor_dev, const uint64_t *nbytes,
+                         const uint64_t *dst_off, int n, void *image, uint64_t image_bytes,
+                         uint64_t *sum_dev, void *stream);
+
 /* Pinned, device-mapped host arena the snapshot lands in (replaces the pageable staging
  * torch.save does implicitly -- reference pyrecover/checkpoint.py:74).  Zero-filled. */
 int pr_host_arena_alloc(uint64_t nbytes, void **host_ptr_out);

@@ -40,6 +40,7 @@ _SIGNATURES = {
     "pr_pack_plan_destroy": (c_int, [c_void_p]),
     "pr_ckpt_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "pr_ckpt_unpack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "pr_ckpt_pack_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_uint64, c_void_p, c_void_p]),
     "pr_host_arena_alloc": (c_int, [c_uint64, POINTER(c_void_p)]),
     "pr_host_arena_free": (c_int, [c_void_p]),
     "pr_host_arena_device_ptr": (c_int, [c_void_p, POINTER(c_void_p)]),

@@ -20,6 +20,7 @@
 #include <unistd.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -422,5 +423,121 @@ extern "C" int pr_file_write_atomic(const char *path, const void *const *pieces,
         unlink(tmp.c_str());
         return PR_ERR_IO;
     }
+    return PR_OK;
+}
+
+// ---- pack without any allocation ------------------------------------------------------------
+// Who needs this: a checkpoint is most valuable exactly when it is hardest to take -- the
+// walltime / preemption handler of a job that has already filled HBM, or a process whose memory
+// manager forbids cudaMalloc after start-up.  pr_pack_plan_create needs a device table (one
+// cudaMalloc, which can fail with the device full and which synchronises the whole device);
+// those callers get the same gather + PR-SUM64 here with the table kept in a fixed array that
+// is part of the library image.
+//
+// The array below is that table.  It costs kNoAllocScratchBytes of global memory on every GPU
+// that loads the library, for the life of the process.  In host code its NAME is only a host-side
+// stand-in -- the device address comes from cudaGetSymbolAddress, looked up once per device with
+// that device current, return code checked, and handed to the kernel as an ordinary pointer.
+namespace {
+
+constexpr int kNoAllocMaxTensors = 1024;
+constexpr uint64_t kNoAllocMaxTiles = 65536;                       // 65536 x 64 KiB = 4 GiB of tiles
+constexpr size_t kNoAllocSegBytes = sizeof(uint64_t) * kNoAllocMaxTensors;
+constexpr size_t kNoAllocScratchBytes = 4 * kNoAllocSegBytes + sizeof(uint32_t) * kNoAllocMaxTiles;   // 288 KiB
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+void *g_noalloc_dev_ptr[kNoAllocMaxDevices] = {};                  // per-device address of the array
+alignas(16) unsigned char g_noalloc_host_table[kNoAllocScratchBytes];   // host image of the table (no malloc)
+int g_noalloc_order[kNoAllocMaxTensors];
+
+}  // namespace
+
+extern "C" int pr_ckpt_pack_noalloc(const void *const *tensor, const uint64_t *nbytes,
+                                    const uint64_t *dst_off, int n, void *image, uint64_t image_bytes,
+                                    uint64_t *sum, void *stream_) {
+    PR_REQUIRE(n >= 0 && (n == 0 || (tensor && nbytes && dst_off)), "pr_ckpt_pack_noalloc: bad table");
+    PR_REQUIRE(n <= kNoAllocMaxTensors,
+               "pr_ckpt_pack_noalloc: %d tensors exceed the built-in table (max %d); use pr_pack_plan_create",
+               n, kNoAllocMaxTensors);
+    if (n == 0) return PR_OK;
+    PR_REQUIRE(image != nullptr && pr_aligned16(image), "pr_ckpt_pack_noalloc: image must be non-NULL and 16-B aligned");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);     // the host table and the device array are shared
+
+    uint64_t *ptrs = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 0 * kNoAllocSegBytes);
+    uint64_t *offs = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 1 * kNoAllocSegBytes);
+    uint64_t *lens = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 2 * kNoAllocSegBytes);
+    uint64_t *first = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 3 * kNoAllocSegBytes);
+    uint32_t *tile_seg = reinterpret_cast<uint32_t *>(g_noalloc_host_table + 4 * kNoAllocSegBytes);
+    uint64_t ntiles = 0;
+    for (int i = 0; i < n; ++i) {
+        PR_REQUIRE(dst_off[i] % 16 == 0, "pr_ckpt_pack_noalloc: dst_off[%d]=%llu is not a multiple of 16", i,
+                   (unsigned long long)dst_off[i]);
+        uint64_t padded = (nbytes[i] + 15) / 16 * 16;
+        PR_REQUIRE(dst_off[i] + padded <= image_bytes,
+                   "pr_ckpt_pack_noalloc: tensor %d (%llu B at %llu) overruns the image (%llu B)", i,
+                   (unsigned long long)nbytes[i], (unsigned long long)dst_off[i], (unsigned long long)image_bytes);
+        PR_REQUIRE(nbytes[i] == 0 || tensor[i] != nullptr, "pr_ckpt_pack_noalloc: tensor %d is NULL", i);
+        uint64_t nt = (nbytes[i] + kTileBytes - 1) / kTileBytes;
+        PR_REQUIRE(ntiles + nt <= kNoAllocMaxTiles,
+                   "pr_ckpt_pack_noalloc: the tensors need more than %llu tiles of %llu KiB (about %llu GiB of payload); "
+                   "use pr_pack_plan_create for larger images",
+                   (unsigned long long)kNoAllocMaxTiles, (unsigned long long)(kTileBytes >> 10),
+                   (unsigned long long)((kNoAllocMaxTiles * kTileBytes) >> 30));
+        ptrs[i] = (uint64_t)(uintptr_t)tensor[i];
+        offs[i] = dst_off[i];
+        lens[i] = nbytes[i];
+        first[i] = ntiles;
+        for (uint64_t t = 0; t < nt; ++t) tile_seg[ntiles + t] = (uint32_t)i;
+        ntiles += nt;
+        g_noalloc_order[i] = i;
+    }
+    std::sort(g_noalloc_order, g_noalloc_order + n, [&](int a, int b) { return offs[a] < offs[b]; });
+    for (int k = 1; k < n; ++k) {
+        int a = g_noalloc_order[k - 1], b = g_noalloc_order[k];
+        PR_REQUIRE(offs[a] + (lens[a] + 15) / 16 * 16 <= offs[b] || lens[a] == 0 || lens[b] == 0,
+                   "pr_ckpt_pack_noalloc: tensors %d and %d overlap in the image", a, b);
+    }
+    if (ntiles == 0) return PR_OK;
+
+    // Set-up, once per device: resolve the device address of the array with this device current.
+    int dev = 0;
+    PR_CUDA(cudaGetDevice(&dev));
+    PR_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "pr_ckpt_pack_noalloc: device ordinal %d unsupported", dev);
+    if (g_noalloc_dev_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        PR_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+        PR_REQUIRE(ptr != nullptr, "pr_ckpt_pack_noalloc: cudaGetSymbolAddress returned NULL");
+        g_noalloc_dev_ptr[dev] = ptr;
+    }
+    unsigned char *base = static_cast<unsigned char *>(g_noalloc_dev_ptr[dev]);
+
+    cudaStream_t stream = (cudaStream_t)stream_;
+    // Every entry the kernel reads ([0, n) of the four tensor arrays, [0, ntiles) of the tile map)
+    // is rewritten here, so nothing in the array has to start at zero and whatever the previous
+    // call left behind its own range is never looked at.  Pageable source: the call returns once
+    // the host table has been consumed, so the next call may overwrite it.
+    for (int part = 0; part < 4; ++part)
+        PR_CUDA(cudaMemcpyAsync(base + part * kNoAllocSegBytes, g_noalloc_host_table + part * kNoAllocSegBytes,
+                                sizeof(uint64_t) * (size_t)n, cudaMemcpyHostToDevice, stream));
+    PR_CUDA(cudaMemcpyAsync(base + 4 * kNoAllocSegBytes, g_noalloc_host_table + 4 * kNoAllocSegBytes,
+                            sizeof(uint32_t) * (size_t)ntiles, cudaMemcpyHostToDevice, stream));
+    PlanDev pd;
+    pd.seg_ptr = reinterpret_cast<const uint64_t *>(base + 0 * kNoAllocSegBytes);
+    pd.seg_off = reinterpret_cast<const uint64_t *>(base + 1 * kNoAllocSegBytes);
+    pd.seg_bytes = reinterpret_cast<const uint64_t *>(base + 2 * kNoAllocSegBytes);
+    pd.tile_first = reinterpret_cast<const uint64_t *>(base + 3 * kNoAllocSegBytes);
+    pd.tile_seg = reinterpret_cast<const uint32_t *>(base + 4 * kNoAllocSegBytes);
+    pd.ntiles = ntiles;
+    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm();
+    int grid = (int)(ntiles < cap ? ntiles : cap);
+    if (sum)
+        pack_kernel<false, true><<<grid, kThreads, 0, stream>>>(pd, (uint8_t *)image, sum);
+    else
+        pack_kernel<false, false><<<grid, kThreads, 0, stream>>>(pd, (uint8_t *)image, nullptr);
+    PR_CUDA(cudaGetLastError());
+    pr_count_launch();
     return PR_OK;
 }
