@@ -43,7 +43,8 @@ def parse():
     ap.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
     ap.add_argument("--preset", type=str, default="1b", choices=["tiny", "1b", "8b"])
     ap.add_argument("--seq", type=int, default=2048)
-    ap.add_argument("--grad-sync", type=str, default="replicated", choices=["replicated", "fused"])
+    ap.add_argument("--grad-sync", type=str, default="fused", choices=["replicated", "fused"])
+    ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around timed leg 1 (for ncu --profile-from-start off)")
     ap.add_argument("--no-ckpt", action="store_true", help="skip the in-region checkpoint snapshot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=8.0, help="target seconds per CPU baseline step")
@@ -187,8 +188,11 @@ def run_b200(a):
     for s in range(a.warmup):
         trainer.step(*dev_batches[s])
     barrier()
-    opt.kernel_events = []
+    timed_owner = trainer.grad_sync if trainer.grad_sync is not None else opt
+    timed_owner.kernel_events = []
     launches_t0 = K.launch_count()
+    if a.profile_range:
+        torch.cuda.cudart().cudaProfilerStart()
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -197,11 +201,13 @@ def run_b200(a):
         maybe_ckpt(s, "dev")
     e1.record()
     barrier()
+    if a.profile_range:
+        torch.cuda.cudart().cudaProfilerStop()
     clocks.stop()
     launches_timed = K.launch_count() - launches_t0
     ms = e0.elapsed_time(e1)
-    k2_ms = [x.elapsed_time(y) for x, y in opt.kernel_events]
-    opt.kernel_events = None
+    k2_ms = [x.elapsed_time(y) for x, y in timed_owner.kernel_events]
+    timed_owner.kernel_events = None
     ckpt.wait_for_checkpoints()
     snap_stats = dict(ckpt._snapshotter(trainer.model, opt).last_stats) if ckpt_at is not None else {}
     del dev_batches
@@ -277,7 +283,16 @@ def run_b200(a):
         hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         arena_elems = opt.arenas[0].numel
         k2_mean = sum(k2_ms) / max(1, len(k2_ms))
-        achieved = 14.0 * arena_elems / (k2_mean * 1e-3) / 1e9 if k2_ms else None
+        fused_multi = world > 1 and a.grad_sync == "fused"
+        # fused K1+K2: every rank updates 1/W of the elements (14 B each) -- reported as HBM GB/s --
+        # and moves N * 2(W-1)/W bus bytes over NVLink in the same launch
+        k2_bytes = 14.0 * arena_elems / (world if fused_multi else 1)
+        achieved = k2_bytes / (k2_mean * 1e-3) / 1e9 if k2_ms else None
+        nvlink = None
+        if fused_multi and k2_ms:
+            bus = 2.0 * arena_elems * 2 * (world - 1) / world / (k2_mean * 1e-3) / 1e9
+            nvlink = {"bus_gbs": bus, "peak_measured_peer_copy": 770.0, "peak_nominal": 900.0,
+                      "frac_of_measured": bus / 770.0, "frac_of_nominal": bus / 900.0}
         traffic = None
         tf = ROOT / "profiles" / "k2_traffic.json"
         if tf.exists():
@@ -294,9 +309,10 @@ def run_b200(a):
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / a.steps, "last_loss": loss_val},
             "gpu_launches": launches_timed,
             "clocks": clocks.summary(),
-            "roofline": {"kernel": "adamw_bf16_kernel<0,false> (K2)", "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
+            "roofline": {"kernel": "allreduce_adamw_kernel<W> (K1+K2 fused)" if fused_multi else "adamw_bf16_kernel<0,false> (K2)",
+                         "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "traffic": traffic,
-                         "peak_source": peak_src, "algorithmic_bytes_per_launch": 14 * arena_elems,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": k2_bytes, "nvlink": nvlink,
                          "launch_ms_mean": k2_mean, "launches_timed": len(k2_ms),
                          "share_of_step": k2_mean / (ms / a.steps)},
             "cpu_baseline": cpu,

@@ -35,7 +35,8 @@ _REGION = {"g": REGION_G, "p": REGION_P, "m": REGION_M, "v": REGION_V}
 
 class GradSync:
     def __init__(self, process_group=None, mode: str = "replicated", bucket_bytes: int = 256 << 20,
-                 overlap: bool = True, max_blocks: int = 0, comm: Optional[K.Comm] = None):
+                 overlap: bool = True, max_blocks: int = 0, overlap_blocks: int = 32,
+                 comm: Optional[K.Comm] = None):
         import torch.distributed as dist
         if mode not in ("replicated", "fused"):
             raise ValueError("mode must be 'replicated' or 'fused'")
@@ -51,6 +52,9 @@ class GradSync:
         self.bucket_bytes = int(bucket_bytes)
         self.overlap = overlap and mode == "replicated"
         self.max_blocks = max_blocks
+        # CTAs of a bucket allreduce that runs UNDER backward: NVLink saturates with a few dozen
+        # CTAs, and every CTA taken is an SM the backward GEMMs cannot use
+        self.overlap_blocks = overlap_blocks
         self.arena: Optional[FlatArena] = None
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.comm_stream = torch.cuda.Stream(device=self.device)
@@ -116,7 +120,7 @@ class GradSync:
             self.comm_stream.wait_event(ev)
             esize = self.arena.layout.esize
             self.comm.allreduce(REGION_G, b["lo"] * esize, (b["hi"] - b["lo"]) * esize, self.arena.dtype,
-                                1.0 / self.world, max_blocks=self.max_blocks, stream=self.comm_stream)
+                                1.0 / self.world, max_blocks=self.overlap_blocks, stream=self.comm_stream)
             self._next_bucket += 1
 
     # ---- called by B200AdamW.step() ---------------------------------------------------------
@@ -131,12 +135,20 @@ class GradSync:
     def reduce_and_step(self, *, lr, beta1, beta2, eps, weight_decay, step, numerics) -> None:
         arena = self.arena
         cur = torch.cuda.current_stream()
+        events = getattr(self, "kernel_events", None)          # bench.py: CUDA events around the update kernel
+        if events is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         if self.mode == "fused" and self.world > 1:
             if numerics != 0 or arena.dtype != torch.bfloat16:
                 raise RuntimeError("fused GradSync implements bf16 arenas with fp32 op-math (fused=True)")
             args = K.adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0 / self.world)
+            if events is not None:
+                e0.record(cur)
             self.comm.allreduce_adamw(REGION_G, REGION_P, REGION_M, REGION_V, 0, arena.numel, args,
                                       max_blocks=self.max_blocks, stream=cur)
+            if events is not None:
+                e1.record(cur)
+                events.append((e0, e1))
             self._moments_replicated = False
         else:
             if self.world > 1:
@@ -148,8 +160,13 @@ class GradSync:
                 else:
                     self.comm.allreduce(REGION_G, 0, arena.layout.nbytes, arena.dtype, 1.0 / self.world,
                                         max_blocks=self.max_blocks, stream=cur)
+            if events is not None:
+                e0.record(cur)
             K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
                      weight_decay=weight_decay, step=step, numerics=numerics)
+            if events is not None:
+                e1.record(cur)
+                events.append((e0, e1))
         # re-arm for the next backward
         self._seen = 0
         self._next_bucket = 0
