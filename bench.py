@@ -22,6 +22,7 @@ flat AdamW update (K2) and -- once, in the middle of the timed region -- a check
 import argparse
 import json
 import os
+import shutil
 import sys
 import tempfile
 import threading
@@ -209,7 +210,7 @@ def run_b200(a):
     k2_ms = [x.elapsed_time(y) for x, y in timed_owner.kernel_events]
     timed_owner.kernel_events = None
     ckpt.wait_for_checkpoints()
-    snap_stats = dict(ckpt._snapshotter(trainer.model, opt).last_stats) if ckpt_at is not None else {}
+    shutil.rmtree(ckpt_dir / f"dev_r{rank}", ignore_errors=True)     # 6 GB per checkpoint: do not fill the disk
     del dev_batches
 
     # ---------------- leg 2: end to end through the public step (host batches) ----------------
@@ -225,6 +226,7 @@ def run_b200(a):
     barrier()
     e2e_s = time.perf_counter() - t0
     ckpt.wait_for_checkpoints()
+    shutil.rmtree(ckpt_dir / f"e2e_r{rank}", ignore_errors=True)
     h2d = sum(t.numel() * t.element_size() for t in host_batches[0])
 
     # ---------------- max over ranks ------------------------------------------------------------
@@ -260,6 +262,7 @@ def run_b200(a):
         ckpt.wait_for_checkpoints()
         durable_s = time.perf_counter() - t_save0
         st = ckpt._snapshotter(trainer.model, opt).last_stats
+        shutil.rmtree(ckpt_dir / f"stall_r{rank}", ignore_errors=True)
         med = sorted(x[1] for x in base)[len(base) // 2]
         stall_ms = max(0.0, withs[3][1] - med)
         ck = {"stall_ms": stall_ms, "stall_frac_of_step": stall_ms / med, "step_ms": med,
@@ -321,6 +324,7 @@ def run_b200(a):
         print(json.dumps(line), flush=True)
     trainer.close()
     ckpt.release_checkpoint_engines()
+    shutil.rmtree(ckpt_dir, ignore_errors=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
