@@ -15,6 +15,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kUnroll = 2;
+constexpr int kMinBlocks = 4;    // <= 64 registers per thread: 32 resident warps per SM
 
 template <bool GRAD_F32>
 __device__ __forceinline__ void load_grad8(const void *g_, uint64_t j, float (&g)[8]) {
@@ -30,10 +31,18 @@ __device__ __forceinline__ void load_grad8(const void *g_, uint64_t j, float (&g
     }
 }
 
+template <int NUMERICS>
+__device__ __forceinline__ void update_vec8(uint4 &P, const float (&g)[8], uint4 &M, uint4 &V,
+                                            const AdamWConsts &c, const AdamWFast &f) {
+    if (NUMERICS == 0) adamw_vec8_fast(P, g, M, V, f);
+    else adamw_vec8<NUMERICS>(P, g, M, V, c);
+}
+
 template <int NUMERICS, bool GRAD_F32>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
 adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__restrict__ m,
                   uint4 *__restrict__ v, uint64_t nvec, AdamWConsts c) {
+    const AdamWFast f = make_adamw_fast(c);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
     // main loop: kUnroll full vectors per thread, all 4*kUnroll loads issued before any math
@@ -51,7 +60,7 @@ adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__r
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
             const uint64_t j = i + u * stride;
-            adamw_vec8<NUMERICS>(P[u], g[u], M[u], V[u], c);
+            update_vec8<NUMERICS>(P[u], g[u], M[u], V[u], c, f);
             st_stream(p + j, P[u]);
             st_stream(m + j, M[u]);
             st_stream(v + j, V[u]);
@@ -61,7 +70,7 @@ adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__r
         uint4 P = ld_stream(p + i), M = ld_stream(m + i), V = ld_stream(v + i);
         float g[8];
         load_grad8<GRAD_F32>(g_, i, g);
-        adamw_vec8<NUMERICS>(P, g, M, V, c);
+        update_vec8<NUMERICS>(P, g, M, V, c, f);
         st_stream(p + i, P);
         st_stream(m + i, M);
         st_stream(v + i, V);

@@ -211,6 +211,7 @@ allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac) 
     const uint64_t poff = goff;
     uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
     uint4 *__restrict__ v = reinterpret_cast<uint4 *>(c.mom2[rank] + goff);
+    const AdamWFast fast = make_adamw_fast(ac);
     xbarrier(c, rank, 0);
     uint64_t lo, hi;
     slice_bounds(nvec, W, rank, lo, hi);
@@ -225,7 +226,7 @@ allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac) 
         acc.zero();
 #pragma unroll
         for (int r = 0; r < W; ++r) acc.add(G[r]);
-        adamw_vec8<0>(P, acc.a, M, V, ac);      // 1/W rides in ac.gscale
+        adamw_vec8_fast(P, acc.a, M, V, fast);  // 1/W rides in ac.gscale
         st_stream(m + i, M);
         st_stream(v + i, V);
 #pragma unroll

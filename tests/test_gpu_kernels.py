@@ -72,6 +72,37 @@ def test_adamw_bf16_vs_oracle_ragged(cuda_lib, oracle, n, numerics):
     assert np.array_equal(_bits(vc), vb)
 
 
+@pytest.mark.parametrize("numerics", [0, 1])
+def test_adamw_edge_values_vs_oracle(cuda_lib, oracle, numerics):
+    """Zeros, subnormal-range moments, huge / inf / NaN gradients: the vectors that leave the
+    branch-free fast path of K2 must still match the oracle bit for bit (NaN-ness for NaNs)."""
+    from pyrecover_b200 import kernels as K
+    specials = [0.0, -0.0, 1e-45, 1e-40, 1e-38, 1e-35, 1e-30, 1e-25, 1e-20, 1e-10, 1e-3, 1.0, 1e10, 1e19, 3e38,
+                float("inf"), float("-inf"), float("nan")]
+    sp = torch.tensor(specials)
+    n = len(specials)
+    # every (g, m, v) combination of the specials, plus a block of ordinary values so that good and
+    # bad elements share 16-byte vectors
+    gi, mi, vi = torch.meshgrid(torch.arange(n), torch.arange(n), torch.arange(n), indexing="ij")
+    g = sp[gi.flatten()].bfloat16()
+    m = sp[mi.flatten()].bfloat16()
+    v = sp[vi.flatten()].abs().bfloat16()
+    gen = torch.Generator().manual_seed(3)
+    mix = torch.rand(g.numel(), generator=gen) < 0.5
+    g = torch.where(mix, (torch.randn(g.numel(), generator=gen) * 1e-3).bfloat16(), g)
+    p = (torch.randn(g.numel(), generator=gen) * 0.02).bfloat16()
+    pc, gc, mc, vc = p.cuda(), g.cuda(), m.cuda(), v.cuda()
+    K.adamw_(pc, gc, mc, vc, lr=1e-3, step=3, numerics=numerics)
+    pb, mb, vb = _bits(p), _bits(m), _bits(v)
+    oracle.adamw_bf16(pb, _bits(g), mb, vb, lr=1e-3, step=3, mode=numerics)
+    for got, want, name in ((pc, pb, "p"), (mc, mb, "m"), (vc, vb, "v")):
+        got = _bits(got)
+        nan_g = (got & 0x7fff) > 0x7f80
+        nan_w = (want & 0x7fff) > 0x7f80
+        assert np.array_equal(nan_g, nan_w), f"{name}: NaN-ness differs"
+        assert np.array_equal(got[~nan_g], want[~nan_w]), f"{name}: {(got[~nan_g] != want[~nan_w]).sum()} elements differ"
+
+
 def test_adamw_unaligned_views(cuda_lib, oracle):
     """Arenas that start 2 bytes off a 16-byte boundary take the element-wise path."""
     from pyrecover_b200 import kernels as K
