@@ -72,6 +72,19 @@ typedef struct pr_adamw_args {
 int pr_adamw(void *p_dev, const void *g_dev, void *m_dev, void *v_dev, uint64_t n,
              int dtype, const pr_adamw_args *args, void *stream);
 
+/* K2 reading every tensor's gradient from where autograd left it (world size 1: no exchange
+ * needs the gradients in one buffer, so the copy into a flat g arena is skipped -- the reference's
+ * optimizer.step() reads p.grad in place too, train.py:274).  The plan fixes the layout: tensor i
+ * occupies elements [elem_off[i], elem_off[i] + numel[i]) of the p / m / v arenas (elem_off a
+ * multiple of 8).  grad_dev[i] is a HOST array entry holding the DEVICE pointer of tensor i's
+ * contiguous bf16 gradient (16-B aligned).  Same arithmetic as pr_adamw. */
+typedef struct pr_adamw_plan pr_adamw_plan;
+int pr_adamw_plan_create(const uint64_t *elem_off, const uint64_t *numel, int n_tensors,
+                         uint64_t arena_elems, pr_adamw_plan **plan_out);
+int pr_adamw_plan_destroy(pr_adamw_plan *plan);
+int pr_adamw_scattered(const pr_adamw_plan *plan, void *p_dev, const void *const *grad_dev,
+                       void *m_dev, void *v_dev, const pr_adamw_args *args, void *stream);
+
 /* ---------------------------------------------------------------- K3: checkpoint -----
  * PR-SUM64, the on-GPU checksum that stands in for hashlib.md5 over the file -- reference
  * pyrecover/checkpoint.py:79-80 (save) and :162-163 (load).  The byte stream is read as

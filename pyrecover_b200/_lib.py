@@ -35,6 +35,9 @@ _SIGNATURES = {
     "pr_launch_count": (c_uint64, []),
     "pr_adamw": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_uint64, c_int,
                          POINTER(AdamWArgs), c_void_p]),
+    "pr_adamw_plan_create": (c_int, [c_void_p, c_void_p, c_int, c_uint64, POINTER(c_void_p)]),
+    "pr_adamw_plan_destroy": (c_int, [c_void_p]),
+    "pr_adamw_scattered": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(AdamWArgs), c_void_p]),
     "pr_checksum": (c_int, [c_void_p, c_uint64, c_uint64, c_void_p, c_void_p]),
     "pr_pack_plan_create": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_uint64, POINTER(c_void_p)]),
     "pr_pack_plan_destroy": (c_int, [c_void_p]),

@@ -9,6 +9,8 @@
 // 28 B per fp32 element.  Each thread owns 16-byte vectors (8 bf16 / 4 fp32 elements) of
 // the four arenas, UNROLL vectors per grid-stride iteration, so 4*UNROLL independent 16-B
 // loads are in flight per thread; the grid is a whole number of CTAs per SM.
+#include <vector>
+
 #include "adamw_math.cuh"
 
 namespace {
@@ -116,6 +118,74 @@ __global__ void adamw_scalar_kernel(void *p_, const void *g_, void *m_, void *v_
     }
 }
 
+// ---- K2 with gradients left where autograd allocated them -----------------------------------
+// At world size 1 nothing needs the gradients in one buffer, so copying 147-291 tensors into the
+// g arena first (2 B read + 2 B write per parameter) is pure overhead: this variant reads tensor
+// s's gradient from its own pointer.  p / m / v stay flat.  Work is cut into tiles of kTileElems
+// that never straddle tensors (device table built once per layout); the per-launch gradient
+// pointers travel as kernel parameters, so there is no per-step upload to synchronise.
+constexpr int kMaxGradPtrs = 384;
+constexpr uint32_t kTileElems = 16384;
+
+struct GradPtrs { const void *ptr[kMaxGradPtrs]; };
+
+struct AdamWPlanDev {
+    const uint64_t *elem_off;     // tensor -> first element in the arenas
+    const uint64_t *numel;
+    const uint64_t *tile_first;   // tensor -> its first tile
+    const uint32_t *tile_seg;     // tile -> tensor
+};
+
+template <int NUMERICS>
+__global__ void __launch_bounds__(kThreads, kMinBlocks)
+adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, uint16_t *__restrict__ v,
+                            AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
+                            const __grid_constant__ GradPtrs gp, AdamWConsts c) {
+    const AdamWFast f = make_adamw_fast(c);
+    for (uint64_t t = tile_lo + blockIdx.x; t < tile_hi; t += gridDim.x) {
+        const uint32_t s = pd.tile_seg[t];
+        const uint64_t off = (t - pd.tile_first[s]) * kTileElems;
+        const uint64_t left = pd.numel[s] - off;
+        const uint32_t n = left < kTileElems ? (uint32_t)left : kTileElems;
+        const uint64_t base = pd.elem_off[s] + off;            // multiple of 8: slots are 256-B aligned
+        uint4 *P = reinterpret_cast<uint4 *>(p + base);
+        uint4 *M = reinterpret_cast<uint4 *>(m + base);
+        uint4 *V = reinterpret_cast<uint4 *>(v + base);
+        const uint16_t *gs = reinterpret_cast<const uint16_t *>(gp.ptr[s - seg_lo]) + off;
+        const uint4 *G = reinterpret_cast<const uint4 *>(gs);
+        const uint32_t nvec = n / 8;
+        uint32_t k = threadIdx.x;
+        for (; k + kThreads < nvec; k += 2 * kThreads) {
+            uint4 Pa = ld_stream(P + k), Ma = ld_stream(M + k), Va = ld_stream(V + k), Ga = ld_stream_nc(G + k);
+            uint4 Pb = ld_stream(P + k + kThreads), Mb = ld_stream(M + k + kThreads), Vb = ld_stream(V + k + kThreads),
+                  Gb = ld_stream_nc(G + k + kThreads);
+            float ga[8], gb[8];
+            unpack_bf8(Ga, ga);
+            unpack_bf8(Gb, gb);
+            update_vec8<NUMERICS>(Pa, ga, Ma, Va, c, f);
+            st_stream(P + k, Pa); st_stream(M + k, Ma); st_stream(V + k, Va);
+            update_vec8<NUMERICS>(Pb, gb, Mb, Vb, c, f);
+            st_stream(P + k + kThreads, Pb); st_stream(M + k + kThreads, Mb); st_stream(V + k + kThreads, Vb);
+        }
+        for (; k < nvec; k += kThreads) {
+            uint4 Pa = ld_stream(P + k), Ma = ld_stream(M + k), Va = ld_stream(V + k), Ga = ld_stream_nc(G + k);
+            float ga[8];
+            unpack_bf8(Ga, ga);
+            update_vec8<NUMERICS>(Pa, ga, Ma, Va, c, f);
+            st_stream(P + k, Pa); st_stream(M + k, Ma); st_stream(V + k, Va);
+        }
+        if (threadIdx.x < (n & 7u)) {       // ragged tail of a tensor whose numel is not a multiple of 8
+            const uint64_t i = base + 8ull * nvec + threadIdx.x;
+            float pf = __uint_as_float((uint32_t)p[i] << 16), mf = __uint_as_float((uint32_t)m[i] << 16);
+            float vf = __uint_as_float((uint32_t)v[i] << 16);
+            float g = __uint_as_float((uint32_t)gs[8u * nvec + threadIdx.x] << 16);
+            if (NUMERICS == 1) adamw_stepwise_bf16(pf, g, mf, vf, c);
+            else adamw_fp32(pf, g, mf, vf, c);
+            p[i] = (uint16_t)f2bf_bits(pf); m[i] = (uint16_t)f2bf_bits(mf); v[i] = (uint16_t)f2bf_bits(vf);
+        }
+    }
+}
+
 int grid_for(uint64_t work_items, int per_block, int blocks_per_sm) {
     uint64_t need = (work_items + per_block - 1) / per_block;
     uint64_t cap = (uint64_t)pr_sm_count() * blocks_per_sm;
@@ -173,6 +243,107 @@ extern "C" int pr_adamw(void *p, const void *g, void *m, void *v, uint64_t n, in
             adamw_scalar_kernel<1><<<grid, 256, 0, stream>>>(p, g, m, v, done, n, dtype, a->grad_dtype, c);
         else
             adamw_scalar_kernel<0><<<grid, 256, 0, stream>>>(p, g, m, v, done, n, dtype, a->grad_dtype, c);
+        PR_CUDA(cudaGetLastError());
+        pr_count_launch();
+    }
+    return PR_OK;
+}
+
+struct pr_adamw_plan {
+    int n = 0;
+    uint64_t arena_elems = 0, ntiles = 0;
+    void *table = nullptr;
+    AdamWPlanDev dev{};
+    std::vector<uint64_t> tile_first;     // host copy, to split launches by tensor range
+};
+
+extern "C" int pr_adamw_plan_create(const uint64_t *elem_off, const uint64_t *numel, int n, uint64_t arena_elems,
+                                    pr_adamw_plan **out) {
+    PR_REQUIRE(out != nullptr, "pr_adamw_plan_create: plan_out is NULL");
+    *out = nullptr;
+    PR_REQUIRE(n > 0 && elem_off && numel, "pr_adamw_plan_create: empty layout");
+    std::vector<uint64_t> first(n + 1);
+    std::vector<uint32_t> tile_seg;
+    for (int i = 0; i < n; ++i) {
+        PR_REQUIRE(elem_off[i] % 8 == 0, "pr_adamw_plan_create: tensor %d starts at element %llu (not 16-B aligned)", i,
+                   (unsigned long long)elem_off[i]);
+        PR_REQUIRE(elem_off[i] + numel[i] <= arena_elems, "pr_adamw_plan_create: tensor %d overruns the arena", i);
+        first[i] = tile_seg.size();
+        tile_seg.insert(tile_seg.end(), (numel[i] + kTileElems - 1) / kTileElems, (uint32_t)i);
+    }
+    first[n] = tile_seg.size();
+    auto *plan = new pr_adamw_plan();
+    plan->n = n;
+    plan->arena_elems = arena_elems;
+    plan->ntiles = tile_seg.size();
+    plan->tile_first = first;
+    const size_t seg = sizeof(uint64_t) * (size_t)n;
+    const size_t total = 3 * seg + sizeof(uint32_t) * tile_seg.size();
+    cudaError_t e = cudaMalloc(&plan->table, total);
+    if (e != cudaSuccess) {
+        delete plan;
+        pr_set_error("pr_adamw_plan_create: cudaMalloc(%zu) failed: %s", total, cudaGetErrorString(e));
+        return PR_ERR_CUDA;
+    }
+    std::vector<uint8_t> host(total);
+    memcpy(host.data(), elem_off, seg);
+    memcpy(host.data() + seg, numel, seg);
+    memcpy(host.data() + 2 * seg, first.data(), seg);
+    memcpy(host.data() + 3 * seg, tile_seg.data(), sizeof(uint32_t) * tile_seg.size());
+    e = cudaMemcpy(plan->table, host.data(), total, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        cudaFree(plan->table);
+        delete plan;
+        pr_set_error("pr_adamw_plan_create: table upload failed: %s", cudaGetErrorString(e));
+        return PR_ERR_CUDA;
+    }
+    uint8_t *b = (uint8_t *)plan->table;
+    plan->dev.elem_off = (const uint64_t *)b;
+    plan->dev.numel = (const uint64_t *)(b + seg);
+    plan->dev.tile_first = (const uint64_t *)(b + 2 * seg);
+    plan->dev.tile_seg = (const uint32_t *)(b + 3 * seg);
+    *out = plan;
+    return PR_OK;
+}
+
+extern "C" int pr_adamw_plan_destroy(pr_adamw_plan *plan) {
+    if (!plan) return PR_OK;
+    if (plan->table) cudaFree(plan->table);
+    delete plan;
+    return PR_OK;
+}
+
+extern "C" int pr_adamw_scattered(const pr_adamw_plan *plan, void *p, const void *const *grad_dev, void *m, void *v,
+                                  const pr_adamw_args *a, void *stream_) {
+    PR_REQUIRE(plan && p && grad_dev && m && v && a, "pr_adamw_scattered: NULL argument");
+    PR_REQUIRE(a->grad_dtype == PR_BF16 && (a->numerics == 0 || a->numerics == 1) && a->step >= 1,
+               "pr_adamw_scattered: bf16 gradients, numerics 0/1 and step >= 1 are required");
+    PR_REQUIRE(pr_aligned16(p) && pr_aligned16(m) && pr_aligned16(v), "pr_adamw_scattered: arenas must be 16-B aligned");
+    for (int i = 0; i < plan->n; ++i)
+        PR_REQUIRE(grad_dev[i] != nullptr && pr_aligned16(grad_dev[i]),
+                   "pr_adamw_scattered: gradient %d is NULL or not 16-B aligned", i);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    AdamWConsts c = make_adamw_consts(a);
+    static int blocks_per_sm = [] {
+        const char *e = getenv("PR_ADAMW_BLOCKS_PER_SM");
+        int b = e ? atoi(e) : 4;
+        return b > 0 ? b : 4;
+    }();
+    for (int s0 = 0; s0 < plan->n; s0 += kMaxGradPtrs) {
+        const int s1 = s0 + kMaxGradPtrs < plan->n ? s0 + kMaxGradPtrs : plan->n;
+        GradPtrs gp;
+        memset(&gp, 0, sizeof(gp));
+        for (int s = s0; s < s1; ++s) gp.ptr[s - s0] = grad_dev[s];
+        const uint64_t t0 = plan->tile_first[s0], t1 = plan->tile_first[s1];
+        if (t1 == t0) continue;
+        uint64_t cap = (uint64_t)pr_sm_count() * blocks_per_sm;
+        int grid = (int)((t1 - t0) < cap ? (t1 - t0) : cap);
+        if (a->numerics == 1)
+            adamw_bf16_scattered_kernel<1><<<grid, kThreads, 0, stream>>>((uint16_t *)p, (uint16_t *)m, (uint16_t *)v,
+                                                                         plan->dev, t0, t1, (uint32_t)s0, gp, c);
+        else
+            adamw_bf16_scattered_kernel<0><<<grid, kThreads, 0, stream>>>((uint16_t *)p, (uint16_t *)m, (uint16_t *)v,
+                                                                         plan->dev, t0, t1, (uint32_t)s0, gp, c);
         PR_CUDA(cudaGetLastError());
         pr_count_launch();
     }

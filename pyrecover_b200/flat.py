@@ -78,15 +78,17 @@ class FlatArena:
         self.dtype, self.device = dtype, device
         self.layout = FlatLayout([p.shape for p in params], dtype, multiple_of=world)
         n = self.layout.numel
+        self._alloc = alloc
+        self._g = None if alloc is None else alloc("g", n, dtype)   # communication buffer: eager
+        self._g_views = None
         if alloc is None:
             def alloc(name, numel, dt):
                 return torch.zeros(numel, dtype=dt, device=device)
+            self._alloc = alloc
         self.p = alloc("p", n, dtype)
-        self.g = alloc("g", n, dtype)
         self.m = alloc("m", n, dtype)
         self.v = alloc("v", n, dtype)
         self.p_views = self.layout.views(self.p)
-        self.g_views = self.layout.views(self.g)
         self.m_views = self.layout.views(self.m)
         self.v_views = self.layout.views(self.v)
         with torch.no_grad():
@@ -97,6 +99,20 @@ class FlatArena:
     @property
     def numel(self) -> int:
         return self.layout.numel
+
+    @property
+    def g(self) -> torch.Tensor:
+        """Flat gradient arena.  At world size 1 K2 reads gradients in place, so it is only
+        allocated when something asks for it (a non-contiguous gradient, the flat K2 path)."""
+        if self._g is None:
+            self._g = self._alloc("g", self.layout.numel, self.dtype)
+        return self._g
+
+    @property
+    def g_views(self) -> List[torch.Tensor]:
+        if self._g_views is None:
+            self._g_views = self.layout.views(self.g)
+        return self._g_views
 
     def gather_grads(self) -> bool:
         """Copy every p.grad that is not already the arena view into the g arena (one
@@ -113,6 +129,22 @@ class FlatArena:
         if src:
             torch._foreach_copy_(dst, src)
         return complete
+
+    def grads_in_place(self):
+        """Per-tensor gradient tensors for the scattered-gradient K2: p.grad itself when it is a
+        contiguous, 16-byte aligned tensor of the arena dtype, else a copy in the g arena slot.
+        Returns None when some parameter has no gradient."""
+        out = []
+        for i, q in enumerate(self.params):
+            g = q.grad
+            if g is None:
+                return None
+            if g.dtype != self.dtype or not g.is_contiguous() or (g.data_ptr() & 15):
+                gv = self.g_views[i]
+                gv.copy_(g)
+                g = gv
+            out.append(g)
+        return out
 
     def named_slots(self, names: Sequence[str]) -> Dict[str, Slot]:
         return {n: s for n, s in zip(names, self.layout.slots)}

@@ -58,6 +58,40 @@ def adamw_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, *
                          ctypes.byref(a), stream_ptr(stream)), "pr_adamw")
 
 
+class AdamWPlan:
+    """Layout of a flat arena for the scattered-gradient K2 (pr_adamw_plan)."""
+
+    def __init__(self, elem_offsets: Sequence[int], numels: Sequence[int], arena_elems: int):
+        n = len(numels)
+        self.n = n
+        offs = (c_uint64 * n)(*[int(o) for o in elem_offsets])
+        lens = (c_uint64 * n)(*[int(x) for x in numels])
+        self._h = c_void_p()
+        check(lib().pr_adamw_plan_create(offs, lens, n, int(arena_elems), ctypes.byref(self._h)), "pr_adamw_plan_create")
+        self._ptrs = (c_void_p * n)()
+
+    def step(self, p: torch.Tensor, grads: Sequence[torch.Tensor], m: torch.Tensor, v: torch.Tensor, *, lr, beta1=0.9,
+             beta2=0.999, eps=1e-8, weight_decay=0.01, step=1, grad_scale=1.0, numerics=0, stream=None) -> None:
+        """grads[i]: contiguous, 16-B aligned bf16 CUDA tensor holding tensor i's gradient."""
+        _require_cuda(p, m, v)
+        for i, g in enumerate(grads):
+            self._ptrs[i] = g.data_ptr()
+        a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, _lib.PR_BF16)
+        check(lib().pr_adamw_scattered(self._h, p.data_ptr(), self._ptrs, m.data_ptr(), v.data_ptr(), ctypes.byref(a),
+                                       stream_ptr(stream)), "pr_adamw_scattered")
+
+    def close(self) -> None:
+        if self._h:
+            lib().pr_adamw_plan_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 # ------------------------------------------------------------------------- K3 checksum --
 
 def checksum_into(t: torch.Tensor, sum_dev: torch.Tensor, word_base: int = 0, stream=None) -> None:

@@ -44,6 +44,8 @@ class B200AdamW(torch.optim.Optimizer):
         self._arenas: List[FlatArena] = []
         self._steps: List[int] = []
         self._step_tensors: List[torch.Tensor] = []
+        self._plans: List[Optional[K.AdamWPlan]] = []
+        self.in_place_grads = True       # False: always gather gradients into the flat g arena first
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad,
                         maximize=maximize, foreach=foreach, capturable=capturable,
                         differentiable=differentiable, fused=fused, decoupled_weight_decay=True)
@@ -62,6 +64,7 @@ class B200AdamW(torch.optim.Optimizer):
         else:
             arena = FlatArena(params)
         self._arenas.append(arena)
+        self._plans.append(None)
         self._steps.append(0)
         # one shared scalar per group: every parameter of the reference steps in lock-step
         step_t = torch.zeros((), dtype=torch.float32)
@@ -90,7 +93,7 @@ class B200AdamW(torch.optim.Optimizer):
             with torch.enable_grad():
                 loss = closure()
         fence = getattr(self, "_snapshot_fence", None)
-        if fence is not None:      # a direct-mode checkpoint is still reading the live arenas
+        if fence is not None:      # a checkpoint snapshot may still be reading the live arenas
             torch.cuda.current_stream().wait_event(fence)
             self._snapshot_fence = None
         for gi, group in enumerate(self.param_groups):
@@ -112,15 +115,27 @@ class B200AdamW(torch.optim.Optimizer):
             if not all(have):
                 raise RuntimeError("B200AdamW: some parameters have no gradient; the flat arena updates "
                                    "all parameters of a group together (reference: find_unused_parameters=False)")
-            arena.gather_grads()
             self._steps[gi] += 1
             self._step_tensors[gi].fill_(self._steps[gi])
             events = getattr(self, "kernel_events", None)      # bench.py: CUDA events around K2
+            scattered = arena.dtype == torch.bfloat16 and self.in_place_grads
+            grads = arena.grads_in_place() if scattered else None
+            if not scattered:
+                arena.gather_grads()
             if events is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-            K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
-                     weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group))
+            if scattered:
+                # world size 1: read every gradient where autograd left it -- no copy into the g arena
+                if self._plans[gi] is None:
+                    self._plans[gi] = K.AdamWPlan([s.offset for s in arena.layout.slots],
+                                                  [s.numel for s in arena.layout.slots], arena.numel)
+                self._plans[gi].step(arena.p, grads, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2,
+                                     eps=group["eps"], weight_decay=group["weight_decay"], step=self._steps[gi],
+                                     numerics=self._numerics(group))
+            else:
+                K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
+                         weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group))
             if events is not None:
                 e1.record()
                 events.append((e0, e1))

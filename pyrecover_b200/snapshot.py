@@ -7,15 +7,14 @@ load path (:182-199, :352-356).
 
 Timeline of one save:
 
-    training stream : ... optimizer.step | K3 pack+checksum (HBM->HBM, ~ms) | next forward ...
-    side stream     :                     wait E1 | D2H image -> pinned arena (PCIe) | E2
-    writer thread   :                                        wait E2 | file write, fsync,
-                                                             rename, side-cars, rotation
+    training stream : ... optimizer.step | next forward + backward ...      | wait E1 | optimizer.step
+    side stream     :          wait | K3 pack+checksum (HBM->HBM, ~ms) E1 | D2H image -> pinned arena E2
+    writer thread   :                                             wait E2 | file write, fsync, rename, ...
 
-`save_*` returns once the pack kernel and the copies are ENQUEUED: the snapshot is consistent
-(stream order puts the pack between this step's optimizer update and the next one), the
-training stream is only occupied for the pack kernel, and durability is awaited by the next
-save / load / `wait()`.
+`save_*` returns once the pack kernel and the copies are ENQUEUED on the side stream: the
+snapshot is consistent (it is ordered after this step's optimizer update, and the NEXT optimizer
+update is fenced on E1 -- forward and backward only read parameters), the training stream never
+waits for it in practice, and durability is awaited by the next save / load / `wait()`.
 
 Two images exist per (model, optimizer): the FULL image (vanilla .pt file: p | m | v arenas +
 stray tensors, one record per dtype) and the SHARD image (sharded directory format: this rank's
@@ -75,31 +74,36 @@ class Image:
         self.sum_host = torch.zeros(2, dtype=torch.int64).pin_memory()
         self.e_copied: Optional[torch.cuda.Event] = None
 
-    def stage(self, side: torch.cuda.Stream) -> torch.cuda.Event:
-        """Pack (+PR-SUM64) on the current stream, D2H on `side`.  Returns the copy-done event."""
+    def stage(self, side: torch.cuda.Stream):
+        """Everything runs on `side`, ordered after the work already queued on the training
+        stream: pack (+PR-SUM64) into the staging image, then the D2H into the pinned arena.
+        Returns (e_read, e_copied): once e_read has fired the live tensors may be modified again
+        (the caller fences the next optimizer step on it -- forward/backward never write them, so
+        the training stream itself does not wait); e_copied = pinned arena complete."""
         main = torch.cuda.current_stream(self.device)
-        if self.e_copied is not None:
-            main.wait_event(self.e_copied)      # the staging image may still be draining
-        self.sum_dev.zero_()
-        e_packed = torch.cuda.Event()
+        e_ready = torch.cuda.Event()
+        e_ready.record(main)
+        side.wait_event(e_ready)
+        # stream order on `side` also keeps this pack behind the previous snapshot's D2H
+        with torch.cuda.stream(side):
+            self.sum_dev.zero_()
+        e_read = torch.cuda.Event()
         if self.staging is not None:
-            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=main)
-            e_packed.record(main)
-            side.wait_event(e_packed)
+            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side)
+            e_read.record(side)
             K.copy_d2h_async(self.host.ptr, self.staging, self.image_bytes, COPY_CHUNK, stream=side)
         else:                                    # direct: copy engines read the live tensors
-            e_packed.record(main)
-            side.wait_event(e_packed)
             for p in self.pieces:
                 if p.nbytes:
                     K.checksum_into(p.tensor.reshape(-1), self.sum_dev, p.img_off // 4, stream=side)
                     K.copy_d2h_async(self.host.ptr + p.img_off, p.tensor, p.nbytes, COPY_CHUNK, stream=side)
+            e_read.record(side)
         with torch.cuda.stream(side):
             self.sum_host.copy_(self.sum_dev, non_blocking=True)
         e = torch.cuda.Event()
         e.record(side)
         self.e_copied = e
-        return e
+        return e_read, e
 
     def checksum(self) -> Tuple[int, int]:
         a, b = self.sum_host.tolist()
@@ -256,8 +260,9 @@ class Snapshotter:
         self._writer.start()
 
     def _fence_optimizer(self, e: torch.cuda.Event) -> None:
-        if self.mode == "direct":            # live arenas must not change before they were read
-            self.optimizer._snapshot_fence = e
+        # the live arenas must not change before the snapshot has read them: the next
+        # optimizer.step() waits for this event (a whole forward+backward later)
+        self.optimizer._snapshot_fence = e
 
     # ------------------------------------------------------------------ vanilla (.pt) -----
     def save_vanilla(self, path: str, state: Dict[str, Any], verify: bool, max_keep: int,
@@ -267,8 +272,8 @@ class Snapshotter:
         t0 = time.perf_counter()
         self.wait()                          # the pinned arena is about to be overwritten
         img = self.full()
-        e_copied = img.stage(self.side)
-        self._fence_optimizer(e_copied)
+        e_read, e_copied = img.stage(self.side)
+        self._fence_optimizer(e_read)
         small: Dict[torch.dtype, list] = {}
         frozen = self.stubify(state, small)
         small_bufs = {dt: torch.cat(parts) for dt, parts in small.items()}
@@ -333,8 +338,8 @@ class Snapshotter:
         t0 = time.perf_counter()
         self.wait()
         img = self.shard(rank, world)
-        e_copied = img.stage(self.side)
-        self._fence_optimizer(e_copied)
+        e_read, e_copied = img.stage(self.side)
+        self._fence_optimizer(e_read)
         small_state = _to_cpu(small_state)
         d = Path(dirpath)
         self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
