@@ -240,34 +240,38 @@ def run_b200(a):
     # ---------------- checkpoint stall, measured on its own (after the timed legs) -------------
     ck = None
     if ckpt_at is not None:
-        def timed_steps(n, with_save):
-            evs = []
-            for i in range(n):
-                a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                torch.cuda.current_stream().synchronize()   # the training stream only: the side
-                w0 = time.perf_counter()                    # stream keeps draining the snapshot
-                a0.record()
-                trainer.step(*dev_small[i % len(dev_small)])
-                if with_save and i == n // 2:
-                    ckpt.save_ckpt_vanilla(trainer.model, opt, trainer.lr_scheduler, None, 900 + i, 1,
-                                           ckpt_dir / f"stall_r{rank}" / f"ckpt_{900 + i}.pt", max_keep=1,
-                                           verify=False, is_distributed=False, rank=0)
-                a1.record()
-                a1.synchronize()
-                evs.append((a0.elapsed_time(a1), (time.perf_counter() - w0) * 1e3))
-            return evs
+        # blocks of 8 steps timed with CUDA events on the training stream, no host sync inside:
+        # A = no checkpoint, B = one checkpoint after the 4th step, A again.  stall = t(B) - mean t(A):
+        # what the snapshot costs the training stream, including the HBM / PCIe traffic it shares.
         dev_small = [tuple(t.to(device) for t in data.batch(5000 + s)) for s in range(4)]
         (ckpt_dir / f"stall_r{rank}").mkdir(parents=True, exist_ok=True)
-        base = timed_steps(6, False)
+
+        def block(with_save):
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            a0.record()
+            for i in range(8):
+                trainer.step(*dev_small[i % len(dev_small)])
+                if with_save and i == 3:
+                    ckpt.save_ckpt_vanilla(trainer.model, opt, trainer.lr_scheduler, None, 900, 1,
+                                           ckpt_dir / f"stall_r{rank}" / "ckpt_900.pt", max_keep=1,
+                                           verify=False, is_distributed=False, rank=0)
+            a1.record()
+            a1.synchronize()
+            return a0.elapsed_time(a1)
+        block(False)
+        tA1 = block(False)
         t_save0 = time.perf_counter()
-        withs = timed_steps(6, True)
+        tB = block(True)
         ckpt.wait_for_checkpoints()
         durable_s = time.perf_counter() - t_save0
+        tA2 = block(False)
         st = ckpt._snapshotter(trainer.model, opt).last_stats
         shutil.rmtree(ckpt_dir / f"stall_r{rank}", ignore_errors=True)
-        med = sorted(x[1] for x in base)[len(base) // 2]
-        stall_ms = max(0.0, withs[3][1] - med)
-        ck = {"stall_ms": stall_ms, "stall_frac_of_step": stall_ms / med, "step_ms": med,
+        step_ms = 0.5 * (tA1 + tA2) / 8
+        stall_ms = max(0.0, tB - 0.5 * (tA1 + tA2))
+        ck = {"stall_ms": stall_ms, "stall_frac_of_step": stall_ms / step_ms, "step_ms": step_ms,
+              "block_ms": {"no_ckpt": [tA1, tA2], "with_ckpt": tB}, "durable_s": durable_s,
               "image_bytes": st.get("image_bytes"), "file_bytes": st.get("file_bytes"),
               "d2h_wait_s": st.get("d2h_wait_s"), "write_s": st.get("write_s"),
               "write_gbs": (st["file_bytes"] / st["write_s"] / 1e9) if st.get("write_s") else None,
