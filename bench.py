@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--impl", type=str, default="b200", choices=["b200", "reference"])
     ap.add_argument("--preset", type=str, default="1b", choices=["tiny", "1b", "8b"])
     ap.add_argument("--seq", type=int, default=2048)
-    ap.add_argument("--grad-sync", type=str, default="fused", choices=["replicated", "fused"])
+    ap.add_argument("--grad-sync", type=str, default="fused", choices=["replicated", "fused", "overlap"])
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around timed leg 1 (for ncu --profile-from-start off)")
     ap.add_argument("--no-ckpt", action="store_true", help="skip the in-region checkpoint snapshot")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -292,7 +292,7 @@ def run_b200(a):
         hbm_peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
         arena_elems = opt.arenas[0].numel
         k2_mean = sum(k2_ms) / max(1, len(k2_ms))
-        fused_multi = world > 1 and a.grad_sync == "fused"
+        fused_multi = world > 1 and a.grad_sync in ("fused", "overlap")
         # fused K1+K2: every rank updates 1/W of the elements (14 B each) -- reported as HBM GB/s --
         # and moves N * 2(W-1)/W bus bytes over NVLink in the same launch
         k2_bytes = 14.0 * arena_elems / (world if fused_multi else 1)

@@ -14,7 +14,15 @@ allreduce its Reducer fires inside `loss.backward()` (train.py:269):
     all their gradients have landed (in bucket order, like the Reducer), overlapping the rest
     of backward; optimizer.step() then runs K2 over the whole arena on every rank;
   * mode "fused": optimizer.step() runs ONE kernel: reduce-scatter -> AdamW on the rank's
-    slice -> all-gather of the updated parameters (moments are sharded across ranks).
+    slice -> all-gather of the updated parameters (moments are sharded across ranks);
+  * mode "overlap": the same fused kernel, but per bucket and launched from the hooks on a side
+    stream WHILE backward is still running: by the time a bucket's last gradient has landed, the
+    autograd nodes that read those parameters have already produced their input gradients
+    (weight and input gradients come out of the same node), and a peer can only push new
+    parameter values into this rank's arena after this rank's own kernel for that bucket has
+    reached the begin barrier.  Only the last bucket's exchange is exposed.  Requires that no
+    parameter is used twice in the graph (no weight tying, no recomputation) -- true for the
+    reference model -- and one backward per step.
 
 The mean's 1/W is applied after the fp32 sum (one rounding), not before in bf16 as the
 Reducer does (reducer.hpp:500) -- strictly more accurate, bounded in tests/.
@@ -38,8 +46,8 @@ class GradSync:
                  overlap: bool = True, max_blocks: int = 0, overlap_blocks: int = 32,
                  comm: Optional[K.Comm] = None):
         import torch.distributed as dist
-        if mode not in ("replicated", "fused"):
-            raise ValueError("mode must be 'replicated' or 'fused'")
+        if mode not in ("replicated", "fused", "overlap"):
+            raise ValueError("mode must be 'replicated', 'fused' or 'overlap'")
         self.mode = mode
         self.pg = process_group
         if comm is not None:                       # emulated / injected communicator (tests)
@@ -50,7 +58,7 @@ class GradSync:
             self.rank, self.world = dist.get_rank(process_group), dist.get_world_size(process_group)
             self.comm = K.Comm(self.rank, self.world)
         self.bucket_bytes = int(bucket_bytes)
-        self.overlap = overlap and mode == "replicated"
+        self.overlap = (overlap and mode == "replicated") or mode == "overlap"
         self.max_blocks = max_blocks
         # CTAs of a bucket allreduce that runs UNDER backward: NVLink saturates with a few dozen
         # CTAs, and every CTA taken is an SM the backward GEMMs cannot use
@@ -63,10 +71,17 @@ class GradSync:
         self._next_bucket = 0
         self._seen = 0
         self._moments_replicated = True
+        self._hyper = None            # callable -> dict(lr, beta1, beta2, eps, weight_decay, step) of the NEXT update
+
+    def bind_hyperparams(self, fn, optimizer=None) -> None:
+        """B200AdamW hands over a callable giving the hyper-parameters of the update that the
+        running backward feeds (mode "overlap" launches the update from the hooks)."""
+        self._hyper = fn
+        self._optimizer = optimizer
 
     # ---- arena allocation: the symmetric tensors come from the communicator ----------------
     def alloc(self, name: str, numel: int, dtype: torch.dtype) -> torch.Tensor:
-        symmetric = name == "g" or self.mode == "fused"
+        symmetric = name == "g" or self.mode in ("fused", "overlap")
         if not symmetric:
             return torch.zeros(numel, dtype=dtype, device=self.device)
         nbytes = numel * torch.empty((), dtype=dtype).element_size()
@@ -119,8 +134,19 @@ class GradSync:
             ev.record(torch.cuda.current_stream())
             self.comm_stream.wait_event(ev)
             esize = self.arena.layout.esize
-            self.comm.allreduce(REGION_G, b["lo"] * esize, (b["hi"] - b["lo"]) * esize, self.arena.dtype,
-                                1.0 / self.world, max_blocks=self.overlap_blocks, stream=self.comm_stream)
+            if self.mode == "overlap":
+                fence = getattr(getattr(self, "_optimizer", None), "_snapshot_fence", None)
+                if fence is not None:      # a checkpoint snapshot may still be reading p / m / v
+                    self.comm_stream.wait_event(fence)
+                h = self._hyper()
+                args = K.adamw_args(h["lr"], h["beta1"], h["beta2"], h["eps"], h["weight_decay"], h["step"],
+                                    grad_scale=1.0 / self.world)
+                self.comm.allreduce_adamw(REGION_G, REGION_P, REGION_M, REGION_V, b["lo"], b["hi"] - b["lo"], args,
+                                          max_blocks=self.overlap_blocks, stream=self.comm_stream)
+                self._moments_replicated = False
+            else:
+                self.comm.allreduce(REGION_G, b["lo"] * esize, (b["hi"] - b["lo"]) * esize, self.arena.dtype,
+                                    1.0 / self.world, max_blocks=self.overlap_blocks, stream=self.comm_stream)
             self._next_bucket += 1
 
     # ---- called by B200AdamW.step() ---------------------------------------------------------
@@ -138,7 +164,19 @@ class GradSync:
         events = getattr(self, "kernel_events", None)          # bench.py: CUDA events around the update kernel
         if events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        if self.mode == "fused" and self.world > 1:
+        if self.mode == "overlap" and self.world > 1:
+            if numerics != 0 or arena.dtype != torch.bfloat16:
+                raise RuntimeError("overlap GradSync implements bf16 arenas with fp32 op-math (fused=True)")
+            if events is not None:
+                e0.record(cur)
+            self._launch_ready_buckets()          # normally a no-op: every bucket was launched by the hooks
+            ev = torch.cuda.Event()
+            ev.record(self.comm_stream)
+            cur.wait_event(ev)
+            if events is not None:
+                e1.record(cur)
+                events.append((e0, e1))
+        elif self.mode == "fused" and self.world > 1:
             if numerics != 0 or arena.dtype != torch.bfloat16:
                 raise RuntimeError("fused GradSync implements bf16 arenas with fp32 op-math (fused=True)")
             args = K.adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0 / self.world)
@@ -179,10 +217,14 @@ class GradSync:
     def replicate_moments(self) -> None:
         """All-gather the per-rank moment slices so every rank holds full m, v (needed before a
         rank-0 vanilla checkpoint: reference save_ckpt_vanilla, pyrecover/checkpoint.py:58-74)."""
-        if self.mode == "fused" and self.world > 1 and not self._moments_replicated:
-            nbytes = self.arena.layout.nbytes
-            self.comm.allgather_slices(REGION_M, 0, nbytes, max_blocks=self.max_blocks)
-            self.comm.allgather_slices(REGION_V, 0, nbytes, max_blocks=self.max_blocks)
+        if self.mode in ("fused", "overlap") and self.world > 1 and not self._moments_replicated:
+            esize = self.arena.layout.esize
+            # ownership follows the launches: one slice set over the whole arena ("fused") or one
+            # per bucket ("overlap")
+            ranges = [(0, self.arena.numel)] if self.mode == "fused" else [(b["lo"], b["hi"]) for b in self._buckets]
+            for lo, hi in ranges:
+                self.comm.allgather_slices(REGION_M, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
+                self.comm.allgather_slices(REGION_V, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
             self._moments_replicated = True
 
     def moments_loaded(self) -> None:

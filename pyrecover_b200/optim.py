@@ -61,6 +61,12 @@ class B200AdamW(torch.optim.Optimizer):
                 raise NotImplementedError("GradSync supports a single param group (as the reference uses)")
             arena = FlatArena(params, world=self._grad_sync.world, alloc=self._grad_sync.alloc)
             self._grad_sync.attach(arena)
+
+            def next_update_hyper(group=group):
+                b1, b2 = group["betas"]
+                return dict(lr=float(group["lr"]), beta1=b1, beta2=b2, eps=group["eps"],
+                            weight_decay=group["weight_decay"], step=self._steps[0] + 1)
+            self._grad_sync.bind_hyperparams(next_update_hyper, self)
         else:
             arena = FlatArena(params)
         self._arenas.append(arena)

@@ -30,7 +30,7 @@ def _launch(tmp, name, steps, world, extra=()):
     return r
 
 
-@pytest.mark.parametrize("mode", ["replicated", "fused"])
+@pytest.mark.parametrize("mode", ["replicated", "fused", "overlap"])
 @pytest.mark.parametrize("sharded", [False, True])
 def test_two_gpu_train_resume_weight_equality(tmp_path, mode, sharded):
     """W = 2 over NVLink: 20 steps straight vs 10 + resume to 20 -> final weights equal with

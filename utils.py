@@ -65,8 +65,9 @@ _ADDITIVE_FLAGS = [
     ("--vocab-size", dict(type=int, default=None, help="default: tokenizer.vocab_size (131072 with --synthetic-data)")),
     ("--device", dict(type=str, default=None, choices=[None, "cuda", "cpu"], help="default: cuda when available")),
     ("--dist-backend", dict(type=str, default=None, choices=[None, "nccl", "gloo"])),
-    ("--grad-sync", dict(type=str, default="replicated", choices=["replicated", "fused"],
-                         help="replicated: P2P allreduce + AdamW on every rank; fused: reduce-scatter+AdamW+all-gather")),
+    ("--grad-sync", dict(type=str, default="replicated", choices=["replicated", "fused", "overlap"],
+                         help="replicated: P2P allreduce + AdamW on every rank; fused: one reduce-scatter+AdamW+all-gather "
+                              "kernel after backward; overlap: the fused kernel per bucket, under backward")),
     ("--snapshot-mode", dict(type=str, default=None, choices=[None, "staged", "direct"])),
     ("--sync-checkpoints", dict(action="store_true", help="wait for each checkpoint to be durable before continuing")),
 ]
