@@ -93,7 +93,9 @@ def write_archive(path: str, pickle_bytes: bytes, records: Sequence[Tuple[str, A
     """Write `<path>.tmp` then rename to `path` (atomic: a walltime kill mid-save can no longer
     leave a corrupt "latest", reference defect pyrecover/checkpoint.py:74).
 
-    records: (key, buffer) pairs; buffer is a bytes-like (memoryview of the pinned arena).
+    records: (key, buffer) pairs; buffer is a bytes-like (memoryview of the pinned arena) or a
+    (total_bytes, iterator of bytes-likes) pair -- the iterator form lets the writer thread
+    stream the image chunk by chunk while later chunks are still crossing PCIe.
     Returns {"md5": hex or None, "offsets": {key: file offset of the record's data}, "bytes": n}.
     """
     path = str(path)
@@ -103,15 +105,25 @@ def write_archive(path: str, pickle_bytes: bytes, records: Sequence[Tuple[str, A
     with open(tmp, "wb") as raw:
         with zipfile.ZipFile(raw, "w", compression=zipfile.ZIP_STORED, allowZip64=True) as zf:
             def put(name: str, data, big_ok: bool = True):
-                mv = memoryview(data).cast("B")
-                zip64 = mv.nbytes >= (1 << 31)
+                if isinstance(data, tuple):
+                    total, chunks = data
+                else:
+                    mv = memoryview(data).cast("B")
+                    total = mv.nbytes
+                    chunks = (mv[o:o + WRITE_CHUNK] for o in range(0, total, WRITE_CHUNK))
+                zip64 = total >= (1 << 31)
                 zi = zipfile.ZipInfo(f"{stem}/{name}", date_time=(1980, 1, 1, 0, 0, 0))
                 zi.compress_type = zipfile.ZIP_STORED
+                zi.file_size = total
                 zi.extra = _padding_extra(raw.tell(), zi.filename, zip64)
                 with zf.open(zi, "w", force_zip64=zip64) as w:
                     data_off = raw.tell()
-                    for o in range(0, mv.nbytes, WRITE_CHUNK):
-                        w.write(mv[o:o + WRITE_CHUNK])
+                    written = 0
+                    for chunk in chunks:
+                        w.write(chunk)
+                        written += memoryview(chunk).nbytes
+                    if written != total:
+                        raise IOError(f"record {name}: wrote {written} of {total} bytes")
                 return data_off
             put("data.pkl", pickle_bytes)
             put("byteorder", b"little")

@@ -75,24 +75,26 @@ class Image:
         self.e_copied: Optional[torch.cuda.Event] = None
 
     def stage(self, side: torch.cuda.Stream):
-        """Everything runs on `side`, ordered after the work already queued on the training
-        stream: pack (+PR-SUM64) into the staging image, then the D2H into the pinned arena.
-        Returns (e_read, e_copied): once e_read has fired the live tensors may be modified again
-        (the caller fences the next optimizer step on it -- forward/backward never write them, so
-        the training stream itself does not wait); e_copied = pinned arena complete."""
+        """Runs on `side`, ordered after the work already queued on the training stream: pack
+        (+PR-SUM64) into the staging image.  Returns e_read: once it has fired the live tensors
+        may be modified again (the caller fences the next optimizer step on it -- forward and
+        backward never write them, so the training stream itself does not wait).
+
+        Staged mode does NOT enqueue the D2H here: the writer thread drains the staging image
+        chunk by chunk at the pace of the file write (`drain`).  A back-to-back 6 GB D2H would
+        saturate PCIe for ~110 ms and, measured on B200, slow the training stream by half of that
+        (kernel launches travel over the same link); the disk is 40x slower than PCIe anyway."""
         main = torch.cuda.current_stream(self.device)
         e_ready = torch.cuda.Event()
         e_ready.record(main)
         side.wait_event(e_ready)
-        # stream order on `side` also keeps this pack behind the previous snapshot's D2H
         with torch.cuda.stream(side):
             self.sum_dev.zero_()
         e_read = torch.cuda.Event()
         if self.staging is not None:
             self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side)
             e_read.record(side)
-            K.copy_d2h_async(self.host.ptr, self.staging, self.image_bytes, COPY_CHUNK, stream=side)
-        else:                                    # direct: copy engines read the live tensors
+        else:                                    # direct: copy engines read the live tensors, all at once
             for p in self.pieces:
                 if p.nbytes:
                     K.checksum_into(p.tensor.reshape(-1), self.sum_dev, p.img_off // 4, stream=side)
@@ -102,8 +104,36 @@ class Image:
             self.sum_host.copy_(self.sum_dev, non_blocking=True)
         e = torch.cuda.Event()
         e.record(side)
-        self.e_copied = e
+        self.e_copied = e            # direct: whole image on the host; staged: checksum on the host
         return e_read, e
+
+    def drain(self, side: torch.cuda.Stream, lo: int = 0, hi: Optional[int] = None):
+        """Generator over memoryviews of the pinned arena covering image bytes [lo, hi), in
+        order.  Staged mode: each chunk is copied D2H on `side` just before it is handed out, with
+        the NEXT chunk's copy already in flight (the consumer's file write overlaps it).  Called
+        from the writer thread."""
+        hi = self.image_bytes if hi is None else hi
+        if self.staging is None:                 # direct mode: stage() already copied everything
+            self.e_copied.synchronize()
+            for o in range(lo, hi, COPY_CHUNK):
+                yield self.host.view(o, min(COPY_CHUNK, hi - o))
+            return
+        torch.cuda.set_device(self.device)
+        self.e_copied.synchronize()              # pack finished
+        spans = [(o, min(COPY_CHUNK, hi - o)) for o in range(lo, hi, COPY_CHUNK)]
+
+        def issue(span):
+            o, n = span
+            K.copy_d2h_async(self.host.ptr + o, self.staging[o:o + n], n, 0, stream=side)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            return ev
+        pending = issue(spans[0]) if spans else None
+        for i, (o, n) in enumerate(spans):
+            ev = pending
+            pending = issue(spans[i + 1]) if i + 1 < len(spans) else None
+            ev.synchronize()
+            yield self.host.view(o, n)
 
     def checksum(self) -> Tuple[int, int]:
         a, b = self.sum_host.tolist()
@@ -284,7 +314,8 @@ class Snapshotter:
             t1 = time.perf_counter()
             e_copied.synchronize()
             t2 = time.perf_counter()
-            records = [(key, img.host.view(r["off"], r["nbytes"])) for key, r in self.records.items()]
+            records = [(key, (r["nbytes"], img.drain(self.side, r["off"], r["off"] + r["nbytes"])))
+                       for key, r in self.records.items()]
             refs = {}
             for i, (dt, buf) in enumerate(small_bufs.items()):
                 key = f"s{i}"
@@ -349,7 +380,12 @@ class Snapshotter:
             d.mkdir(parents=True, exist_ok=True)
             e_copied.synchronize()
             t2 = time.perf_counter()
-            K.file_write_atomic(str(d / f"shard_{rank:05d}.bin"), [(img.host.ptr, img.image_bytes)])
+            shard_path = d / f"shard_{rank:05d}.bin"
+            with open(str(shard_path) + ".tmp", "wb", buffering=0) as f:
+                for chunk in img.drain(self.side):
+                    f.write(chunk)
+                os.fsync(f.fileno())
+            os.replace(str(shard_path) + ".tmp", str(shard_path))
             A, B = img.checksum()
             side = {"format": SHARD_FORMAT, "rank": rank, "world": world, "sum64": [A, B],
                     "image_bytes": img.image_bytes, "full_image_bytes": self.full_bytes,
