@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-budget-s", type=float, default=8.0, help="target seconds per CPU baseline step")
     ap.add_argument("--ckpt-dir", type=str, default=None)
+    ap.add_argument("--ckpt-format", type=str, default=None, choices=[None, "vanilla", "sharded"],
+                    help="default: vanilla at N=1 (rank 0 writes one torch-loadable file), sharded at N>1 (every rank writes 1/N)")
     return ap.parse_args()
 
 
@@ -154,7 +156,8 @@ def run_b200(a):
     vocab = MODEL_PRESETS[a.preset][5]
     torch.manual_seed(0)
     torch.set_default_dtype(torch.bfloat16)
-    model = Transformer(preset_args(a.preset, a.seq)).to(device)
+    with torch.device(device):                      # initialise on the GPU: an 8 B model takes minutes on the host
+        model = Transformer(preset_args(a.preset, a.seq))
     torch.set_default_dtype(torch.float32)
     trainer = Trainer(model, device, lr=1e-5, fused=True, warmup_steps=10, world_size=world, local_rank=local_rank,
                       grad_sync_mode=a.grad_sync)
@@ -170,21 +173,38 @@ def run_b200(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    fmt = a.ckpt_format or ("vanilla" if world == 1 else "sharded")
+
+    def save(tag, step_idx):
+        # the reference-facing API, exactly as train.py calls it (barriers included)
+        if fmt == "sharded":
+            ckpt.save_ckpt_distributed(trainer.model, opt, trainer.lr_scheduler, None, step_idx, 1,
+                                       ckpt_dir / tag / f"ckpt_{step_idx}", max_keep=1, verify=False,
+                                       is_distributed=world > 1, rank=rank)
+        else:
+            ckpt.save_ckpt_vanilla(trainer.model, opt, trainer.lr_scheduler, None, step_idx, 1,
+                                   ckpt_dir / tag / f"ckpt_{step_idx}.pt", max_keep=1, verify=False,
+                                   is_distributed=world > 1, rank=rank)
+
     def maybe_ckpt(step_idx, tag):
         if ckpt_at is not None and step_idx == ckpt_at:
-            ckpt.save_ckpt_vanilla(trainer.model, opt, trainer.lr_scheduler, None, step_idx, 1,
-                                   ckpt_dir / f"{tag}_r{rank}" / f"ckpt_{step_idx}.pt", max_keep=1, verify=False,
-                                   is_distributed=False, rank=0)
+            save(tag, step_idx)
 
     clocks = ClockSampler(local_rank)
     if ckpt_at is not None:
         # staging image + pinned arena are allocated once per job (first checkpoint); do it before timing
-        ckpt._snapshotter(trainer.model, opt).full()
+        snap0 = ckpt._snapshotter(trainer.model, opt)
+        snap0.shard(rank, world) if (a.ckpt_format or ("vanilla" if world == 1 else "sharded")) == "sharded" else \
+            (snap0.full() if rank == 0 else None)
 
     # ---------------- leg 1: device-resident inputs, CUDA-event timed -------------------------
     total = a.warmup + a.steps
     dev_batches = [tuple(t.to(device) for t in data.batch(s)) for s in range(total)]
-    for d in (ckpt_dir / f"dev_r{rank}", ckpt_dir / f"e2e_r{rank}"):
+    if world > 1:      # every rank must see the same directory
+        names = [str(ckpt_dir)]
+        dist.broadcast_object_list(names, src=0)
+        ckpt_dir = Path(names[0])
+    for d in (ckpt_dir / "dev", ckpt_dir / "e2e", ckpt_dir / "stall"):
         d.mkdir(parents=True, exist_ok=True)
     for s in range(a.warmup):
         trainer.step(*dev_batches[s])
@@ -210,7 +230,9 @@ def run_b200(a):
     k2_ms = [x.elapsed_time(y) for x, y in timed_owner.kernel_events]
     timed_owner.kernel_events = None
     ckpt.wait_for_checkpoints()
-    shutil.rmtree(ckpt_dir / f"dev_r{rank}", ignore_errors=True)     # 6 GB per checkpoint: do not fill the disk
+    barrier()
+    if rank == 0:
+        shutil.rmtree(ckpt_dir / "dev", ignore_errors=True)           # GBs per checkpoint: do not fill the disk
     del dev_batches
 
     # ---------------- leg 2: end to end through the public step (host batches) ----------------
@@ -228,7 +250,9 @@ def run_b200(a):
     e2e_s = time.perf_counter() - t0
     loss_val = float(loss_host[total - 1])
     ckpt.wait_for_checkpoints()
-    shutil.rmtree(ckpt_dir / f"e2e_r{rank}", ignore_errors=True)
+    barrier()
+    if rank == 0:
+        shutil.rmtree(ckpt_dir / "e2e", ignore_errors=True)
     h2d = sum(t.numel() * t.element_size() for t in host_batches[0])
 
     # ---------------- max over ranks ------------------------------------------------------------
@@ -244,7 +268,6 @@ def run_b200(a):
         # A = no checkpoint, B = one checkpoint after the 4th step, A again.  stall = t(B) - mean t(A):
         # what the snapshot costs the training stream, including the HBM / PCIe traffic it shares.
         dev_small = [tuple(t.to(device) for t in data.batch(5000 + s)) for s in range(4)]
-        (ckpt_dir / f"stall_r{rank}").mkdir(parents=True, exist_ok=True)
 
         def block(with_save):
             a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -253,9 +276,7 @@ def run_b200(a):
             for i in range(8):
                 trainer.step(*dev_small[i % len(dev_small)])
                 if with_save and i == 3:
-                    ckpt.save_ckpt_vanilla(trainer.model, opt, trainer.lr_scheduler, None, 900, 1,
-                                           ckpt_dir / f"stall_r{rank}" / "ckpt_900.pt", max_keep=1,
-                                           verify=False, is_distributed=False, rank=0)
+                    save("stall", 900)
             a1.record()
             a1.synchronize()
             return a0.elapsed_time(a1)
@@ -267,7 +288,9 @@ def run_b200(a):
         durable_s = time.perf_counter() - t_save0
         tA2 = block(False)
         st = ckpt._snapshotter(trainer.model, opt).last_stats
-        shutil.rmtree(ckpt_dir / f"stall_r{rank}", ignore_errors=True)
+        barrier()
+        if rank == 0:
+            shutil.rmtree(ckpt_dir / "stall", ignore_errors=True)
         step_ms = 0.5 * (tA1 + tA2) / 8
         stall_ms = max(0.0, tB - 0.5 * (tA1 + tA2))
         ck = {"stall_ms": stall_ms, "stall_frac_of_step": stall_ms / step_ms, "step_ms": step_ms,
@@ -275,7 +298,7 @@ def run_b200(a):
               "image_bytes": st.get("image_bytes"), "file_bytes": st.get("file_bytes"),
               "d2h_wait_s": st.get("d2h_wait_s"), "write_s": st.get("write_s"),
               "write_gbs": (st["file_bytes"] / st["write_s"] / 1e9) if st.get("write_s") else None,
-              "mode": ckpt._snapshotter(trainer.model, opt).mode}
+              "mode": ckpt._snapshotter(trainer.model, opt).mode, "format": fmt}
 
     # ---------------- cpu baseline (rank 0, N = 1) -----------------------------------------------
     cpu = None
@@ -313,7 +336,7 @@ def run_b200(a):
             "config": {"workload": WORKLOAD, "params": n_params, "global_batch": world, "seq_len": a.seq,
                        "parallelism": f"dp{world}", "grad_sync": a.grad_sync if world > 1 else "none (N=1)",
                        "l2": "inputs >> L2: four 2 GB arenas streamed once per step",
-                       "checkpoint": "none" if ckpt_at is None else "1 vanilla snapshot inside each timed region (staged pack, async D2H + write)"},
+                       "checkpoint": "none" if ckpt_at is None else f"1 {fmt} snapshot inside each timed region (staged pack on a side stream, D2H + file write in the writer thread)"},
             "e2e": {"value": tokens_per_step * a.steps / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / a.steps, "last_loss": loss_val},
             "gpu_launches": launches_timed,
@@ -330,7 +353,8 @@ def run_b200(a):
         print(json.dumps(line), flush=True)
     trainer.close()
     ckpt.release_checkpoint_engines()
-    shutil.rmtree(ckpt_dir, ignore_errors=True)
+    if rank == 0:
+        shutil.rmtree(ckpt_dir, ignore_errors=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -51,15 +51,18 @@ def main():
     ap.add_argument("--max-log2", type=int, default=30)
     ap.add_argument("--json", type=str, default=None)
     ap.add_argument("--max-blocks", type=int, default=0)
+    ap.add_argument("--fused-max-log2", type=int, default=31, help="largest size for the fused AR+AdamW rows (4 regions)")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     maxb = 1 << a.max_log2
+    fmax = 1 << min(a.max_log2, a.fused_max_log2)
     comm = K.Comm(rank, world)
-    for region in range(4):
-        comm.alloc_region(region, maxb)
+    comm.alloc_region(0, maxb)
+    for region in range(1, 4):
+        comm.alloc_region(region, fmax)
     comm.connect()
     G = comm.region_tensor(0, torch.bfloat16)
     P = comm.region_tensor(1, torch.bfloat16)
@@ -132,6 +135,13 @@ def main():
         t = timed(lambda: dist.all_reduce(buf))
         row["nccl_ms"], row["nccl_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
         step = [0]
+        if nbytes > fmax:
+            results["rows"].append(row)
+            if rank == 0:
+                print(f"{nbytes >> 20:6d} MiB  p2p {row['p2p_ms']:8.3f} ms {row['p2p_busbw']:7.1f} GB/s | "
+                      f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s", flush=True)
+            del buf
+            continue
 
         def fused():
             step[0] += 1

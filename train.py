@@ -87,8 +87,9 @@ def train(args):
     log_rank0("Setting up Model...")
     torch.manual_seed(args.seed)             # identical initial weights on every rank and every run
     Transformer, model_config = model_args_from_cli(args, vocab_size)
-    with set_default_dtype(PRECISION_STR_TO_DTYPE[args.model_dtype]):
-        model = Transformer(model_config).to(device)
+    with set_default_dtype(PRECISION_STR_TO_DTYPE[args.model_dtype]), torch.device(device):
+        model = Transformer(model_config)       # built in place on the device (the reference builds on the
+                                                # host and copies, train.py:100-101: minutes at 8 B)
     if args.compile:
         log_rank0("Using `torch.compile`")
         model = torch.compile(model, fullgraph=True)
