@@ -167,6 +167,9 @@ int pr_file_write_atomic(const char *path, const void *const *pieces_host,
  * 16-byte vectors from all peers, accumulate in fp32 in rank order 0..W-1 (every rank gets
  * bit-identical results), scale, round once and push the result to every rank.
  * NCCL/gloo are used only by the caller, to exchange the export blobs.
+ * With NVSwitch multicast (pr_comm_multicast) the sum is taken by the switch instead: identical on
+ * every rank, but in an unspecified order (summation-order tolerance vs the rank-order sum) and,
+ * for bf16, rounded to bf16 before the scale is applied (exact when the scale is a power of two).
  */
 typedef struct pr_comm pr_comm;
 
@@ -185,8 +188,24 @@ int pr_comm_export(pr_comm *comm, void *blob_out);
 int pr_comm_import(pr_comm *comm, const void *blobs);
 /* 1 in *timed_out if a kernel of this communicator gave up waiting for a peer. */
 int pr_comm_error(pr_comm *comm, int *timed_out);
+/* NVSwitch multicast (NVLS).  Where the driver supports it (and PR_COMM_MULTICAST is not "0" in the
+ * environment at pr_comm_create), regions are CUDA VMM allocations: pr_comm_import then ships them as
+ * POSIX file descriptors over abstract unix sockets instead of CUDA-IPC handles, binds each region
+ * to a multicast object and maps it.  The summing then happens inside the switch -- the job NCCL's
+ * NVLS algorithm does for the reference's DDP allreduce (train.py:110-115 / :269).
+ * policy: -2 = only query, -1 = automatic (use multicast for world >= 4, where it moves fewer bytes
+ * per link than P2P), 0 = never, 1 = whenever available.  *available: the mappings exist;
+ * *in_use: PR_AR_AUTO, pr_allreduce_adamw and pr_allgather_slices take the multicast kernels.
+ * Every rank must choose the same policy.  Either out pointer may be NULL. */
+int pr_comm_multicast(pr_comm *comm, int policy, int *available, int *in_use);
 
-typedef enum pr_ar_algo { PR_AR_AUTO = 0, PR_AR_ONE_SHOT = 1, PR_AR_TWO_SHOT = 2 } pr_ar_algo;
+typedef enum pr_ar_algo {
+    PR_AR_AUTO = 0,       /* one-shot <= 512 KiB, else multimem when pr_comm_multicast says in_use, else two-shot */
+    PR_AR_ONE_SHOT = 1,
+    PR_AR_TWO_SHOT = 2,
+    PR_AR_MULTIMEM = 3    /* NVSwitch in-switch reduction (multimem.ld_reduce / multimem.st); PR_ERR_UNSUPPORTED
+                             when the communicator has no multicast mapping */
+} pr_ar_algo;
 
 /* In-place allreduce of region[offset, offset+nbytes) with result = round(sum * scale).
  * offset and nbytes must be multiples of 16.  max_blocks bounds the grid (0 = one CTA per

@@ -14,7 +14,7 @@ PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libpyrecover_b200.so"
 
 PR_BF16, PR_F32 = 0, 1
-PR_AR_AUTO, PR_AR_ONE_SHOT, PR_AR_TWO_SHOT = 0, 1, 2
+PR_AR_AUTO, PR_AR_ONE_SHOT, PR_AR_TWO_SHOT, PR_AR_MULTIMEM = 0, 1, 2, 3
 PR_MAX_WORLD = 8
 PR_MAX_REGIONS = 4
 PR_EXPORT_BLOB_BYTES = 512
@@ -58,6 +58,7 @@ _SIGNATURES = {
     "pr_comm_export": (c_int, [c_void_p, c_void_p]),
     "pr_comm_import": (c_int, [c_void_p, c_void_p]),
     "pr_comm_error": (c_int, [c_void_p, POINTER(c_int)]),
+    "pr_comm_multicast": (c_int, [c_void_p, c_int, POINTER(c_int), POINTER(c_int)]),
     "pr_allreduce": (c_int, [c_void_p, c_int, c_uint64, c_uint64, c_int, c_float, c_int, c_int, c_void_p]),
     "pr_allreduce_adamw": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_uint64, c_uint64, c_int,
                                    POINTER(AdamWArgs), c_int, c_void_p]),

@@ -27,16 +27,30 @@
 // cooperative launch runs the W ranks as blockIdx.y, with the same flag protocol.  That is
 // how the kernels are tested on a single GPU (separate spinning launches on one GPU are not
 // guaranteed to run concurrently).
+//
+// NVSwitch multicast (NVLS).  When the driver offers it, the symmetric regions are CUDA VMM
+// allocations (shared as POSIX file descriptors instead of CUDA-IPC handles -- fabric.cu) bound
+// to a multicast object, and two more kernels exist: rank r fetches slice r ALREADY SUMMED by
+// the switch (multimem.ld_reduce, fp32 accumulation) and broadcasts the result with one
+// multimem.st.  Per direction a GPU then moves N(1 + 1/W) bytes instead of 2N(W-1)/W: less
+// than the P2P volume from W = 4 up (1.125 N vs 1.75 N at W = 8), more at W = 2 -- so the
+// automatic choice is multicast for W >= 4 and P2P below.  The order in which the switch adds
+// the W contributions is not specified: results are identical on every rank (one rank
+// computes each slice) but equal to the rank-order fp32 sum only within summation-order
+// tolerance, and the bf16 sum is rounded by the switch BEFORE the 1/W scale (exact for W a
+// power of two).
 #include <stdlib.h>
 #include <unistd.h>
 
 #include "adamw_math.cuh"
+#include "fabric.cuh"
 
 namespace {
 
 constexpr int kThreads = 512;
 constexpr int kMaxBlocks = 512;          // flag words are provisioned for this many CTAs
 constexpr int kSlots = 2;
+constexpr int kMulticastBlocks = 64;     // default grid of the multicast kernels (tunable per call: max_blocks)
 constexpr int kOneShotVecPerThread = 4;  // register budget of the one-shot kernel
 constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * PR_MAX_WORLD;
 constexpr uint32_t kBlobMagic = 0x50523142u;  // "PR1B"
@@ -53,6 +67,8 @@ struct CommDev {
     uint8_t *mom1[PR_MAX_WORLD];     // exp_avg region (fused kernel; only the own rank's is touched)
     uint8_t *mom2[PR_MAX_WORLD];     // exp_avg_sq region
     uint32_t *flags[PR_MAX_WORLD];
+    uint8_t *mc_grad;                // multicast mapping of the gradient region (NULL without NVLS)
+    uint8_t *mc_param;               // multicast mapping of the parameter region
 };
 
 __device__ __forceinline__ unsigned long long globaltimer() {
@@ -253,6 +269,127 @@ allgather_slices_kernel(CommDev c, uint64_t off, uint64_t nvec) {
     xbarrier(c, rank, 1);
 }
 
+// ---- NVSwitch multicast kernels ------------------------------------------------------------------
+// multimem.ld_reduce: one request, the switch reads the vector from every bound GPU and returns the
+// sum (bf16x2 inputs accumulated in fp32).  multimem.st: one store, the switch writes every GPU.
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16(const void *mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ uint4 mm_ld_reduce_f32(const void *mc) {
+    float a, b, c, d;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(mc) : "memory");
+    return make_uint4(__float_as_uint(a), __float_as_uint(b), __float_as_uint(c), __float_as_uint(d));
+}
+__device__ __forceinline__ void mm_st(void *mc, const uint4 &v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)),
+                    "f"(__uint_as_float(v.w)) : "memory");
+}
+template <bool F32>
+__device__ __forceinline__ uint4 scale_vec(const uint4 &v, float scale) {
+    uint4 o;
+    const uint32_t *w = &v.x;
+    uint32_t *q = &o.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (F32) q[k] = __float_as_uint(__fmul_rn(__uint_as_float(w[k]), scale));
+        else q[k] = pack_bf2(__fmul_rn(bf_lo(w[k]), scale), __fmul_rn(bf_hi(w[k]), scale));
+    }
+    return o;
+}
+
+template <bool F32>
+__global__ void __launch_bounds__(kThreads, 1)
+allreduce_mc_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
+    const int rank = c.rank;
+    xbarrier(c, rank, 0);
+    uint64_t lo, hi;
+    slice_bounds(nvec, c.world, rank, lo, hi);
+    const uint64_t stride = (uint64_t)gridDim.x * kThreads;
+    uint8_t *base = c.mc_grad + off;
+    constexpr int U = 4;
+    for (uint64_t i = lo + (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < hi; i += U * stride) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint64_t j = i + u * stride;
+            if (j < hi) v[u] = F32 ? mm_ld_reduce_f32(base + 16 * j) : mm_ld_reduce_bf16(base + 16 * j);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint64_t j = i + u * stride;
+            if (j < hi) mm_st(base + 16 * j, scale == 1.0f ? v[u] : scale_vec<F32>(v[u], scale));
+        }
+    }
+    xbarrier(c, rank, 1);
+}
+
+// fused: switch-reduced gradient slice -> AdamW on the local (p, m, v) slice -> multicast store of
+// the updated parameters into every rank's parameter region
+__global__ void __launch_bounds__(kThreads, 1)
+allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac) {
+    const int rank = c.rank;
+    const uint8_t *__restrict__ p = c.param[rank] + goff;
+    uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
+    uint4 *__restrict__ v = reinterpret_cast<uint4 *>(c.mom2[rank] + goff);
+    const uint8_t *mg = c.mc_grad + goff;
+    uint8_t *mp = c.mc_param + goff;
+    const AdamWFast fast = make_adamw_fast(ac);
+    xbarrier(c, rank, 0);
+    uint64_t lo, hi;
+    slice_bounds(nvec, c.world, rank, lo, hi);
+    const uint64_t stride = (uint64_t)gridDim.x * kThreads;
+    constexpr int U = 2;
+    for (uint64_t i = lo + (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < hi; i += U * stride) {
+        uint4 G[U], P[U], M[U], V[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint64_t j = i + u * stride;
+            if (j < hi) {
+                G[u] = mm_ld_reduce_bf16(mg + 16 * j);
+                P[u] = ld_stream(p + 16 * j);
+                M[u] = ld_stream(m + j);
+                V[u] = ld_stream(v + j);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint64_t j = i + u * stride;
+            if (j < hi) {
+                float g[8];
+                const uint32_t *w = &G[u].x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    g[2 * k] = bf_lo(w[k]);
+                    g[2 * k + 1] = bf_hi(w[k]);
+                }
+                adamw_vec8_fast(P[u], g, M[u], V[u], fast);   // 1/W rides in ac.gscale
+                st_stream(m + j, M[u]);
+                st_stream(v + j, V[u]);
+                mm_st(mp + 16 * j, P[u]);
+            }
+        }
+    }
+    xbarrier(c, rank, 1);
+}
+
+// all-gather of per-rank slices through the switch: one multicast store instead of W - 1 pushes
+__global__ void __launch_bounds__(kThreads, 1)
+allgather_slices_mc_kernel(CommDev c, uint64_t off, uint64_t nvec) {
+    const int rank = c.rank;
+    xbarrier(c, rank, 0);
+    uint64_t lo, hi;
+    slice_bounds(nvec, c.world, rank, lo, hi);
+    const uint64_t stride = (uint64_t)gridDim.x * kThreads;
+    for (uint64_t i = lo + (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride)
+        mm_st(c.mc_grad + off + 16 * i, ld_stream(c.grad[rank] + off + 16 * i));
+    xbarrier(c, rank, 1);
+}
+
 struct Blob {
     uint32_t magic;
     int32_t rank;
@@ -260,9 +397,19 @@ struct Blob {
     int32_t pid;
     uint64_t region_bytes[PR_MAX_REGIONS];
     cudaIpcMemHandle_t flags;
-    cudaIpcMemHandle_t region[PR_MAX_REGIONS];
+    cudaIpcMemHandle_t region[PR_MAX_REGIONS];   // unused for VMM regions (those travel as descriptors)
+    int32_t vmm;                                 // regions are VMM allocations shared as file descriptors
+    int32_t want_mc;                             // this rank can and wants to join multicast objects
+    char sock[48];                               // abstract unix socket the descriptors are sent to
 };
 static_assert(sizeof(Blob) <= PR_EXPORT_BLOB_BYTES, "export blob too large");
+
+struct FdMsg {                                   // one datagram per (sender, receiver) pair
+    uint32_t magic;
+    int32_t rank;
+    int32_t n_region_fds;                        // descriptors of the sender's regions, in region order
+    int32_t n_mc_fds;                            // rank 0 only: multicast objects, in region order (after the regions)
+};
 
 }  // namespace
 
@@ -272,11 +419,25 @@ struct pr_comm {
     uint32_t seq = 0;
     int *err_host = nullptr, *err_dev = nullptr;
     unsigned long long timeout_ns = 20ull * 1000000000ull;
-    // [rank][region]; for a real comm only [self] is owned, the rest are IPC mappings
+    // [rank][region]; for a real comm only [self] is owned, the rest are IPC / VMM mappings
     uint8_t *region[PR_MAX_WORLD][PR_MAX_REGIONS] = {};
     uint64_t region_bytes[PR_MAX_REGIONS] = {};
     uint32_t *flags[PR_MAX_WORLD] = {};
+    // NVSwitch multicast state (fabric.cu)
+    bool vmm = false, want_mc = false, mc_ready = false;
+    int mc_policy = -1;                          // -1 auto (W >= 4), 0 never, 1 whenever available
+    PrFabricCaps caps;
+    PrVmmBlock block[PR_MAX_WORLD][PR_MAX_REGIONS];
+    CUmemGenericAllocationHandle mc_handle[PR_MAX_REGIONS] = {};
+    CUdeviceptr mc_va[PR_MAX_REGIONS] = {};
+    bool mc_bound[PR_MAX_REGIONS] = {};
+    PrSock sock;
 };
+
+static bool use_multicast(const pr_comm *c) {
+    if (!c->mc_ready || c->mc_policy == 0) return false;
+    return c->mc_policy == 1 || c->world >= 4;
+}
 
 static int fill_dev(pr_comm *c, int grad_region, int param_region, CommDev &d, int m_region = -1,
                     int v_region = -1) {
@@ -294,6 +455,8 @@ static int fill_dev(pr_comm *c, int grad_region, int param_region, CommDev &d, i
         d.mom2[r] = (r < c->world && v_region >= 0) ? c->region[r][v_region] : nullptr;
         d.flags[r] = r < c->world ? c->flags[r] : nullptr;
     }
+    d.mc_grad = c->mc_ready ? (uint8_t *)c->mc_va[grad_region] : nullptr;
+    d.mc_param = (c->mc_ready && param_region >= 0) ? (uint8_t *)c->mc_va[param_region] : nullptr;
     return PR_OK;
 }
 
@@ -355,6 +518,21 @@ extern "C" int pr_comm_create(int rank, int world, pr_comm **out) {
     PR_CUDA(cudaHostGetDevicePointer((void **)&c->err_dev, c->err_host, 0));
     PR_CUDA(cudaMalloc((void **)&c->flags[rank], kFlagWords * sizeof(uint32_t)));
     PR_CUDA(cudaMemset(c->flags[rank], 0, kFlagWords * sizeof(uint32_t)));
+    // NVSwitch multicast needs the regions to be VMM allocations; PR_COMM_MULTICAST=0 keeps the
+    // cudaMalloc + CUDA-IPC regions (P2P kernels only), =1 uses multicast whenever it is available,
+    // unset = multicast from W = 4 up
+    const char *mc_env = getenv("PR_COMM_MULTICAST");
+    if (mc_env && *mc_env) c->mc_policy = atoi(mc_env) != 0 ? 1 : 0;
+    if (world > 1 && c->mc_policy != 0) {
+        c->caps = pr_fabric_caps(c->device, world);
+        c->vmm = c->caps.driver && c->caps.posix_fd && c->caps.multicast;
+        c->want_mc = c->vmm;
+        if (c->vmm && pr_sock_open(&c->sock, rank) != PR_OK) c->vmm = c->want_mc = false;
+        if (getenv("PR_COMM_DEBUG"))
+            fprintf(stderr, "[pr_comm rank %d] driver %d posix_fd %d multicast %d alloc_gran %zu mc_gran min %zu rec %zu -> vmm %d\n",
+                    rank, (int)c->caps.driver, (int)c->caps.posix_fd, (int)c->caps.multicast, c->caps.alloc_gran,
+                    c->caps.mc_gran_min, c->caps.mc_gran_rec, (int)c->vmm);
+    }
     *out = c;
     return PR_OK;
 }
@@ -382,11 +560,15 @@ extern "C" int pr_comm_create_emulated(int world, pr_comm **out) {
 extern "C" int pr_comm_destroy(pr_comm *c) {
     if (!c) return PR_OK;
     cudaDeviceSynchronize();
+    for (int k = 0; k < PR_MAX_REGIONS; ++k)
+        if (c->mc_handle[k] || c->mc_va[k])
+            pr_mc_detach(c->mc_handle[k], c->device, c->mc_va[k], c->block[c->rank][k].size, c->mc_bound[k]);
     for (int r = 0; r < c->world; ++r) {
         const bool own = c->emulated || r == c->rank;
         for (int k = 0; k < PR_MAX_REGIONS; ++k) {
             if (!c->region[r][k]) continue;
-            if (own) cudaFree(c->region[r][k]);
+            if (c->vmm) pr_vmm_free(&c->block[r][k]);
+            else if (own) cudaFree(c->region[r][k]);
             else cudaIpcCloseMemHandle(c->region[r][k]);
         }
         if (c->flags[r]) {
@@ -394,6 +576,7 @@ extern "C" int pr_comm_destroy(pr_comm *c) {
             else cudaIpcCloseMemHandle(c->flags[r]);
         }
     }
+    pr_sock_close(&c->sock);
     if (c->err_host) cudaFreeHost(c->err_host);
     delete c;
     return PR_OK;
@@ -407,8 +590,16 @@ extern "C" int pr_comm_region_alloc(pr_comm *c, int region, uint64_t nbytes) {
     PR_REQUIRE(nbytes > 0 && nbytes % 16 == 0, "pr_comm_region_alloc: nbytes must be a positive multiple of 16");
     for (int r = 0; r < c->world; ++r) {
         if (!c->emulated && r != c->rank) continue;
-        PR_CUDA(cudaMalloc((void **)&c->region[r][region], nbytes));
-        PR_CUDA(cudaMemset(c->region[r][region], 0, nbytes));
+        if (c->vmm) {
+            const size_t rounded = pr_fabric_round(c->caps, nbytes);
+            int rc = pr_vmm_alloc(c->device, rounded, &c->block[r][region]);
+            if (rc) return rc;
+            c->region[r][region] = (uint8_t *)c->block[r][region].va;
+            PR_CUDA(cudaMemset(c->region[r][region], 0, rounded));
+        } else {
+            PR_CUDA(cudaMalloc((void **)&c->region[r][region], nbytes));
+            PR_CUDA(cudaMemset(c->region[r][region], 0, nbytes));
+        }
     }
     c->region_bytes[region] = nbytes;
     return PR_OK;
@@ -433,12 +624,100 @@ extern "C" int pr_comm_export(pr_comm *c, void *blob_out) {
     b.world = c->world;
     b.pid = (int32_t)getpid();
     PR_CUDA(cudaIpcGetMemHandle(&b.flags, c->flags[c->rank]));
+    b.vmm = c->vmm ? 1 : 0;
+    b.want_mc = c->want_mc ? 1 : 0;
+    memcpy(b.sock, c->sock.name, sizeof(b.sock));
     for (int k = 0; k < PR_MAX_REGIONS; ++k) {
         b.region_bytes[k] = c->region_bytes[k];
-        if (c->region_bytes[k]) PR_CUDA(cudaIpcGetMemHandle(&b.region[k], c->region[c->rank][k]));
+        if (c->region_bytes[k] && !c->vmm) PR_CUDA(cudaIpcGetMemHandle(&b.region[k], c->region[c->rank][k]));
     }
     memset(blob_out, 0, PR_EXPORT_BLOB_BYTES);
     memcpy(blob_out, &b, sizeof(b));
+    return PR_OK;
+}
+
+// VMM regions: every rank sends the descriptors of its regions to every peer over the unix
+// sockets named in the blobs (rank 0 adds the multicast objects it created), then maps what it
+// received and joins the multicast team.  cuMulticastBindMem blocks until all W devices have been
+// added, so returning from here means the whole team is bound.
+static int import_vmm(pr_comm *c, const Blob *blobs) {
+    int nreg = 0, reg_ids[PR_MAX_REGIONS];
+    for (int k = 0; k < PR_MAX_REGIONS; ++k)
+        if (c->region_bytes[k]) reg_ids[nreg++] = k;
+    bool mc = true;
+    for (int r = 0; r < c->world; ++r) mc = mc && blobs[r].want_mc;
+    int fds[2 * PR_MAX_REGIONS], nfds = 0;
+    for (int i = 0; i < nreg; ++i) {
+        int rc = pr_vmm_export_fd(c->block[c->rank][reg_ids[i]], &fds[nfds]);
+        if (rc) return rc;
+        ++nfds;
+    }
+    FdMsg out;
+    out.magic = kBlobMagic;
+    out.rank = c->rank;
+    out.n_region_fds = nreg;
+    out.n_mc_fds = 0;
+    if (mc && c->rank == 0) {
+        for (int i = 0; i < nreg; ++i) {
+            const int k = reg_ids[i];
+            int fd = -1;
+            if (pr_mc_create(c->world, c->block[0][k].size, &c->mc_handle[k], &fd) != PR_OK) {
+                for (int j = 0; j < i; ++j) {            // multicast stays off for the whole team
+                    close(fds[nreg + j]);
+                    pr_mc_detach(c->mc_handle[reg_ids[j]], c->device, 0, 0, false);
+                    c->mc_handle[reg_ids[j]] = 0;
+                }
+                nfds = nreg;
+                out.n_mc_fds = 0;
+                break;
+            }
+            fds[nfds++] = fd;
+            out.n_mc_fds = i + 1;
+        }
+    }
+    int rc = PR_OK;
+    for (int r = 0; r < c->world && rc == PR_OK; ++r)
+        if (r != c->rank) rc = pr_sock_send(c->sock, blobs[r].sock, &out, sizeof(out), fds, nfds);
+    for (int i = 0; i < nfds; ++i) close(fds[i]);
+    if (rc) return rc;
+    int n_mc_seen = c->rank == 0 ? out.n_mc_fds : -1;
+    for (int got = 0; got < c->world - 1; ++got) {
+        FdMsg in;
+        int rfds[16], nr = 0;
+        if ((rc = pr_sock_recv(c->sock, &in, sizeof(in), rfds, 16, &nr, 120 * 1000))) return rc;
+        bool ok = in.magic == kBlobMagic && in.rank >= 0 && in.rank < c->world && in.rank != c->rank &&
+                  in.n_region_fds == nreg && nr == in.n_region_fds + in.n_mc_fds && !c->region[in.rank][reg_ids[0]];
+        for (int i = 0; ok && i < nreg; ++i) {
+            const int k = reg_ids[i];
+            rc = pr_vmm_import_fd(c->device, rfds[i], c->block[c->rank][k].size, &c->block[in.rank][k]);
+            if (rc) ok = false;
+            else c->region[in.rank][k] = (uint8_t *)c->block[in.rank][k].va;
+        }
+        if (ok && in.rank == 0) {
+            n_mc_seen = in.n_mc_fds;
+            for (int i = 0; ok && i < in.n_mc_fds && in.n_mc_fds == nreg; ++i)
+                if ((rc = pr_mc_import(rfds[nreg + i], &c->mc_handle[reg_ids[i]]))) ok = false;
+        }
+        for (int i = 0; i < nr; ++i) close(rfds[i]);
+        if (!ok) {
+            if (rc == PR_OK) {
+                pr_set_error("pr_comm_import: malformed descriptor message from rank %d", in.rank);
+                rc = PR_ERR_STATE;
+            }
+            return rc;
+        }
+    }
+    if (mc && n_mc_seen == nreg && nreg > 0) {
+        for (int i = 0; i < nreg; ++i) {
+            const int k = reg_ids[i];
+            if ((rc = pr_mc_attach(c->mc_handle[k], c->device, c->block[c->rank][k], &c->mc_va[k]))) return rc;
+            c->mc_bound[k] = true;
+        }
+        c->mc_ready = true;
+    }
+    if (getenv("PR_COMM_DEBUG"))
+        fprintf(stderr, "[pr_comm rank %d] %d VMM regions mapped from %d peers, multicast %s\n", c->rank, nreg, c->world - 1,
+                c->mc_ready ? "bound" : "off");
     return PR_OK;
 }
 
@@ -446,8 +725,9 @@ extern "C" int pr_comm_import(pr_comm *c, const void *blobs) {
     PR_REQUIRE(c && blobs, "pr_comm_import: NULL argument");
     PR_REQUIRE(!c->emulated, "pr_comm_import: emulated communicators need no import");
     PR_REQUIRE(!c->imported, "pr_comm_import: already imported");
+    Blob all[PR_MAX_WORLD];
     for (int r = 0; r < c->world; ++r) {
-        Blob b;
+        Blob &b = all[r];
         memcpy(&b, (const uint8_t *)blobs + (size_t)r * PR_EXPORT_BLOB_BYTES, sizeof(b));
         PR_REQUIRE(b.magic == kBlobMagic && b.rank == r && b.world == c->world,
                    "pr_comm_import: blob %d is malformed (magic %08x rank %d world %d)", r, b.magic, b.rank, b.world);
@@ -455,13 +735,32 @@ extern "C" int pr_comm_import(pr_comm *c, const void *blobs) {
             PR_REQUIRE(b.region_bytes[k] == c->region_bytes[k],
                        "pr_comm_import: rank %d region %d is %llu B here but %llu B there", r, k,
                        (unsigned long long)c->region_bytes[k], (unsigned long long)b.region_bytes[k]);
+        PR_REQUIRE((b.vmm != 0) == c->vmm, "pr_comm_import: rank %d %s VMM regions but this rank %s (set PR_COMM_MULTICAST "
+                   "identically on every rank)", r, b.vmm ? "uses" : "does not use", c->vmm ? "does" : "does not");
+        b.sock[sizeof(b.sock) - 1] = 0;
+    }
+    for (int r = 0; r < c->world; ++r) {
         if (r == c->rank) continue;
-        PR_CUDA(cudaIpcOpenMemHandle((void **)&c->flags[r], b.flags, cudaIpcMemLazyEnablePeerAccess));
+        PR_CUDA(cudaIpcOpenMemHandle((void **)&c->flags[r], all[r].flags, cudaIpcMemLazyEnablePeerAccess));
+        if (c->vmm) continue;
         for (int k = 0; k < PR_MAX_REGIONS; ++k)
             if (c->region_bytes[k])
-                PR_CUDA(cudaIpcOpenMemHandle((void **)&c->region[r][k], b.region[k], cudaIpcMemLazyEnablePeerAccess));
+                PR_CUDA(cudaIpcOpenMemHandle((void **)&c->region[r][k], all[r].region[k], cudaIpcMemLazyEnablePeerAccess));
+    }
+    if (c->vmm && c->world > 1) {
+        int rc = import_vmm(c, all);
+        if (rc) return rc;
     }
     c->imported = true;
+    return PR_OK;
+}
+
+extern "C" int pr_comm_multicast(pr_comm *c, int policy, int *available, int *in_use) {
+    PR_REQUIRE(c != nullptr, "pr_comm_multicast: comm is NULL");
+    PR_REQUIRE(policy >= -2 && policy <= 1, "pr_comm_multicast: policy must be -2 (query), -1 (auto), 0 (off) or 1 (on)");
+    if (policy != -2) c->mc_policy = policy;
+    if (available) *available = c->mc_ready ? 1 : 0;
+    if (in_use) *in_use = use_multicast(c) ? 1 : 0;
     return PR_OK;
 }
 
@@ -504,6 +803,16 @@ extern "C" int pr_allreduce(pr_comm *c, int region, uint64_t offset, uint64_t nb
         }
     }
     const void *k = nullptr;
+    if (algo == PR_AR_MULTIMEM || (algo == PR_AR_AUTO && use_multicast(c))) {
+        if (!c->mc_ready) {
+            pr_set_error("pr_allreduce: PR_AR_MULTIMEM asked for, but this communicator has no NVSwitch multicast mapping");
+            return PR_ERR_UNSUPPORTED;
+        }
+        k = f32 ? (const void *)allreduce_mc_kernel<true> : (const void *)allreduce_mc_kernel<false>;
+        // the switch does the summing: a few dozen CTAs keep the links full (4 vectors in flight per thread)
+        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : kMulticastBlocks, k, (nvec + c->world - 1) / c->world / 4 + 1);
+        return launch(c, k, grid, stream, d, offset, nvec, scale);
+    }
     PR_DISPATCH_W(c->world, k = f32 ? (const void *)allreduce_twoshot_kernel<W_, true>
                                     : (const void *)allreduce_twoshot_kernel<W_, false>);
     int grid = pick_grid(c, max_blocks, k, (nvec + c->world - 1) / c->world);
@@ -530,9 +839,14 @@ extern "C" int pr_allreduce_adamw(pr_comm *c, int grad_region, int param_region,
     AdamWConsts ac = make_adamw_consts(a);
     const uint64_t nvec = n / 8;
     const void *k = nullptr;
+    uint64_t goff = elem_offset * 2;
+    if (use_multicast(c)) {
+        k = (const void *)allreduce_adamw_mc_kernel;
+        int grid = pick_grid(c, max_blocks, k, (nvec + c->world - 1) / c->world);
+        return launch(c, k, grid, (cudaStream_t)stream_, d, goff, nvec, ac);
+    }
     PR_DISPATCH_W(c->world, k = (const void *)allreduce_adamw_kernel<W_>);
     int grid = pick_grid(c, max_blocks, k, (nvec + c->world - 1) / c->world);
-    uint64_t goff = elem_offset * 2;
     return launch(c, k, grid, (cudaStream_t)stream_, d, goff, nvec, ac);
 }
 
@@ -545,6 +859,11 @@ extern "C" int pr_allgather_slices(pr_comm *c, int region, uint64_t offset, uint
     if ((rc = fill_dev(c, region, -1, d))) return rc;
     const uint64_t nvec = nbytes / 16;
     const void *k = nullptr;
+    if (use_multicast(c)) {
+        k = (const void *)allgather_slices_mc_kernel;
+        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : kMulticastBlocks, k, (nvec + c->world - 1) / c->world);
+        return launch(c, k, grid, (cudaStream_t)stream_, d, offset, nvec);
+    }
     PR_DISPATCH_W(c->world, k = (const void *)allgather_slices_kernel<W_>);
     int grid = pick_grid(c, max_blocks, k, (nvec + c->world - 1) / c->world);
     return launch(c, k, grid, (cudaStream_t)stream_, d, offset, nvec);

@@ -276,6 +276,13 @@ class Comm:
         check(lib().pr_allgather_slices(self._h, region, offset, nbytes, max_blocks, stream_ptr(stream)),
               "pr_allgather_slices")
 
+    def multicast(self, policy: int = -2):
+        """NVSwitch multicast state -> (available, in_use).  policy -2 only queries; -1 automatic
+        (world >= 4), 0 off, 1 on whenever available (pr_comm_multicast; same choice on every rank)."""
+        av, use = c_int(), c_int()
+        check(lib().pr_comm_multicast(self._h, policy, ctypes.byref(av), ctypes.byref(use)), "pr_comm_multicast")
+        return bool(av.value), bool(use.value)
+
     def timed_out(self) -> bool:
         e = c_int()
         check(lib().pr_comm_error(self._h, ctypes.byref(e)), "pr_comm_error")

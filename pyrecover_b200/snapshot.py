@@ -172,6 +172,7 @@ class Snapshotter:
         self._shard_key = None
         self._writer: Optional[threading.Thread] = None
         self._writer_error: Optional[BaseException] = None
+        self._stub_cache: Dict[Any, PT.TensorStub] = {}
         self.last_stats: Dict[str, Any] = {}
         # ---- full image layout: one record per dtype; arenas first (p | m | v), extras after ----
         by_dtype: "OrderedDict[torch.dtype, List[torch.Tensor]]" = OrderedDict()
@@ -248,20 +249,38 @@ class Snapshotter:
                 return s.record, (s.rec_off + (p - base)) // t.element_size()
         return None
 
+    _ATOMS = (int, float, str, bool, type(None), bytes, complex)
+
     def stubify(self, obj: Any, small: Dict[torch.dtype, list]) -> Any:
         """Replace every tensor of a nested state by a TensorStub.  CUDA tensors inside a piece
         point into the big records; anything else lands in a small per-dtype host record (step
-        scalars, RNG state, ...)."""
+        scalars, RNG state, ...).
+
+        This runs on the TRAINING thread inside save_*: a training loop that is close to
+        launch-bound stalls the GPU by however long it takes, so arena views are resolved through a
+        cache (the layout is static for the job) and the rest is kept allocation-light."""
         if isinstance(obj, torch.Tensor):
-            loc = self._locate(obj) if obj.is_cuda and obj.is_contiguous() else None
-            if loc is not None:
-                rec = PT.RecordRef(loc[0], obj.dtype, self.records[loc[0]]["nbytes"] // obj.element_size())
-                return PT.TensorStub(rec, loc[1], obj.shape)
-            host = obj.detach().to("cpu").contiguous()
-            bucket = small.setdefault(host.dtype, [])
-            off = sum(t.numel() for t in bucket)
-            bucket.append(host.reshape(-1).clone())
-            return _Small(host.dtype, off, tuple(host.shape))
+            if obj.is_cuda:
+                key = (obj.data_ptr(), obj.dtype, obj.shape, obj.stride())
+                stub = self._stub_cache.get(key)
+                if stub is not None:
+                    return stub
+                loc = self._locate(obj) if obj.is_contiguous() else None
+                if loc is not None:
+                    rec = PT.RecordRef(loc[0], obj.dtype, self.records[loc[0]]["nbytes"] // obj.element_size())
+                    stub = PT.TensorStub(rec, loc[1], obj.shape)
+                    self._stub_cache[key] = stub
+                    return stub
+            host = obj.detach().reshape(-1).to("cpu", copy=True)      # strays: a private host copy
+            bucket = small.get(host.dtype)
+            if bucket is None:
+                bucket = small[host.dtype] = [[], 0]
+            off = bucket[1]
+            bucket[0].append(host)
+            bucket[1] = off + host.numel()
+            return _Small(host.dtype, off, tuple(obj.shape))
+        if type(obj) in self._ATOMS:
+            return obj
         if isinstance(obj, dict):
             return type(obj)((k, self.stubify(v, small)) for k, v in obj.items())
         if isinstance(obj, list):
@@ -306,7 +325,7 @@ class Snapshotter:
         self._fence_optimizer(e_read)
         small: Dict[torch.dtype, list] = {}
         frozen = self.stubify(state, small)
-        small_bufs = {dt: torch.cat(parts) for dt, parts in small.items()}
+        small_bufs = {dt: (torch.cat(parts) if len(parts) > 1 else parts[0]) for dt, (parts, _) in small.items()}
         path = str(path)
         self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
 

@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--json", type=str, default=None)
     ap.add_argument("--max-blocks", type=int, default=0)
     ap.add_argument("--fused-max-log2", type=int, default=31, help="largest size for the fused AR+AdamW rows (4 regions)")
+    ap.add_argument("--mc-blocks", type=str, default="32,64,148", help="grid sizes tried for the multicast kernels")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -64,11 +65,15 @@ def main():
     for region in range(1, 4):
         comm.alloc_region(region, fmax)
     comm.connect()
+    mc_avail, mc_auto = comm.multicast()
+    mc_blocks = [int(x) for x in a.mc_blocks.split(",") if x]
+    if rank == 0:
+        print(f"world {world}: NVSwitch multicast available={mc_avail}, automatic choice uses it={mc_auto}", flush=True)
     G = comm.region_tensor(0, torch.bfloat16)
     P = comm.region_tensor(1, torch.bfloat16)
     M = comm.region_tensor(2, torch.bfloat16)
     V = comm.region_tensor(3, torch.bfloat16)
-    results = {"world": world, "rows": []}
+    results = {"world": world, "multicast_available": mc_avail, "multicast_auto": mc_auto, "rows": []}
     scale = 1.0 / world
 
     # ---------------- parity at 8 MiB -----------------------------------------------------------
@@ -94,11 +99,75 @@ def main():
         results[f"parity_{name}"] = bool(flag.item())
         assert flag.item() == 1, f"{name} allreduce differs from the fp32 rank-order sum on some rank"
         dist.barrier()
+    S = torch.stack([t.float().abs() for t in gathered]).sum(0) / world
+    bound = world * 2.0 ** -9 * S + 1e-30
+    if mc_avail:
+        # the switch adds the W contributions in its own order and rounds the bf16 sum before the
+        # scale: identical on every rank, within the summation-order bound of the rank-order sum
+        G[:n].copy_(local_g)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce(0, 0, n * 2, torch.bfloat16, scale, algo=_lib.PR_AR_MULTIMEM)
+        torch.cuda.synchronize()
+        got = G[:n].clone()
+        # bound: one bf16 ulp of the result (the switch's final rounding is not specified to be
+        # round-to-nearest-even) + the fp32 summation-order term
+        exact = acc * scale
+        mc_bound = 2.0 ** -7 * exact.abs() + world * 2.0 ** -23 * S + 1e-30
+        err = (got.float() - exact).abs()
+        within = bool((err <= mc_bound).all())
+        exact = float((got == expect).float().mean())
+        ulp = (got.view(torch.int16).int() - expect.view(torch.int16).int())
+        toward_zero = float(((got.float().abs() <= (acc * scale).abs()) | (got == expect)).float().mean())
+        results["multimem_ulp_diff_hist"] = {str(k): int((ulp == k).sum()) for k in (-2, -1, 0, 1, 2)}
+        results["multimem_fraction_not_above_exact_magnitude"] = toward_zero
+        if rank == 0:
+            bad = (got != expect).nonzero().flatten()[:6].tolist()
+            for i in bad:
+                print(f"  mismatch @{i}: inputs {[hex(t.view(torch.int16)[i].item() & 0xffff) for t in gathered]} "
+                      f"fp32 mean {float(acc[i] * scale):.9e} got {hex(got.view(torch.int16)[i].item() & 0xffff)} "
+                      f"rne {hex(expect.view(torch.int16)[i].item() & 0xffff)}", flush=True)
+            print(f"  ulp-diff histogram {results['multimem_ulp_diff_hist']}, |got| <= |exact| fraction {toward_zero:.4f}", flush=True)
+        allg = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(allg, got)
+        same = all(torch.equal(allg[0], t) for t in allg)
+        flag = torch.tensor([int(within and same)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        results["parity_multimem_within_bound"] = bool(flag.item())
+        results["multimem_identical_across_ranks"] = same
+        results["multimem_fraction_bit_equal_to_rank_order_sum"] = exact
+        if rank == 0:
+            print(f"multimem allreduce: within bound {within}, identical across ranks {same}, bit-equal fraction {exact:.6f}", flush=True)
+        assert flag.item() == 1, "multimem allreduce outside the summation-order bound or differing across ranks"
+        # run-to-run determinism (resume equality depends on it)
+        G[:n].copy_(local_g)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce(0, 0, n * 2, torch.bfloat16, scale, algo=_lib.PR_AR_MULTIMEM, max_blocks=17)
+        torch.cuda.synchronize()
+        results["multimem_deterministic"] = bool(torch.equal(G[:n], got))
+        # fp32 payload
+        Gf = comm.region_tensor(0, torch.float32)
+        nf = n // 2
+        lf = local_g[:nf].float()
+        gf = [torch.empty_like(lf) for _ in range(world)]
+        dist.all_gather(gf, lf)
+        Gf[:nf].copy_(lf)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce(0, 0, nf * 4, torch.float32, scale, algo=_lib.PR_AR_MULTIMEM)
+        torch.cuda.synchronize()
+        ef = torch.zeros(nf, dtype=torch.float32, device=dev)
+        for t in gf:
+            ef = ef + t
+        ef = ef * scale
+        okf = bool(((Gf[:nf] - ef).abs() <= 2.0 ** -22 * world * torch.stack([t.abs() for t in gf]).sum(0) + 1e-30).all())
+        results["parity_multimem_f32"] = okf
+        assert okf, "fp32 multimem allreduce outside the bound"
+        dist.barrier()
     nccl = local_g.clone()
     nccl.mul_(scale)
     dist.all_reduce(nccl)
-    S = torch.stack([t.float().abs() for t in gathered]).sum(0) / world
-    bound = world * 2.0 ** -9 * S + 1e-30
     within = bool(((nccl.float() - expect.float()).abs() <= bound).all())
     results["nccl_within_bound"] = within
     assert within
@@ -108,6 +177,7 @@ def main():
     torch.cuda.synchronize()
     dist.barrier()
     args = K.adamw_args(1e-4, 0.9, 0.999, 1e-8, 0.01, step=1, grad_scale=scale)
+    comm.multicast(0)                               # P2P kernels: bit-exact against the rank-order sum
     comm.allreduce_adamw(0, 1, 2, 3, 0, n, args, max_blocks=a.max_blocks)
     comm.allgather_slices(2, 0, n * 2)
     comm.allgather_slices(3, 0, n * 2)
@@ -120,6 +190,33 @@ def main():
     results["parity_fused"] = bool(flag.item())
     assert flag.item() == 1, "fused allreduce+AdamW differs from allreduce -> AdamW"
     dist.barrier()
+    if mc_avail:
+        # multicast fused kernel == (multimem allreduce -> pr_adamw on the result), bit for bit
+        comm.multicast(1)
+        G[:n].copy_(local_g)
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce(0, 0, n * 2, torch.bfloat16, 1.0, algo=_lib.PR_AR_MULTIMEM)
+        torch.cuda.synchronize()
+        gsum = G[:n].clone()
+        pr, mr, vr = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+        K.adamw_(pr, gsum, mr, vr, lr=1e-4, step=1, grad_scale=scale)
+        G[:n].copy_(local_g); P[:n].copy_(p0); M[:n].zero_(); V[:n].zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        comm.allreduce_adamw(0, 1, 2, 3, 0, n, args, max_blocks=a.max_blocks)
+        comm.allgather_slices(2, 0, n * 2)
+        comm.allgather_slices(3, 0, n * 2)
+        torch.cuda.synchronize()
+        ok = torch.equal(P[:n], pr) and torch.equal(M[:n], mr) and torch.equal(V[:n], vr)
+        flag = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        results["parity_fused_multimem"] = bool(flag.item())
+        if rank == 0:
+            print(f"fused multimem AR+AdamW == multimem AR -> AdamW: {bool(flag.item())}", flush=True)
+        assert flag.item() == 1, "multicast fused allreduce+AdamW differs from multimem allreduce -> AdamW"
+        dist.barrier()
+    comm.multicast(-1)
 
     # ---------------- bandwidth sweep -----------------------------------------------------------
     for lg in range(a.min_log2, a.max_log2 + 1):
@@ -127,8 +224,14 @@ def main():
         ne = nbytes // 2
         buf = torch.empty(ne, dtype=torch.bfloat16, device=dev).normal_(0, 1e-3)
         row = {"bytes": nbytes}
-        t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, max_blocks=a.max_blocks))
+        t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, algo=_lib.PR_AR_TWO_SHOT, max_blocks=a.max_blocks))
         row["p2p_ms"], row["p2p_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        if mc_avail:
+            for nb in mc_blocks:
+                t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, algo=_lib.PR_AR_MULTIMEM, max_blocks=nb))
+                row[f"mc{nb}_ms"], row[f"mc{nb}_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+            best = min(mc_blocks, key=lambda nb: row[f"mc{nb}_ms"])
+            row["mc_ms"], row["mc_busbw"], row["mc_best_blocks"] = row[f"mc{best}_ms"], row[f"mc{best}_busbw"], best
         if nbytes <= (4 << 20):
             t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, algo=_lib.PR_AR_ONE_SHOT))
             row["oneshot_ms"] = t
@@ -139,7 +242,8 @@ def main():
             results["rows"].append(row)
             if rank == 0:
                 print(f"{nbytes >> 20:6d} MiB  p2p {row['p2p_ms']:8.3f} ms {row['p2p_busbw']:7.1f} GB/s | "
-                      f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s", flush=True)
+                      + (f"multimem {row['mc_ms']:8.3f} ms {row['mc_busbw']:7.1f} GB/s ({row['mc_best_blocks']} CTAs) | " if mc_avail else "")
+                      + f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s", flush=True)
             del buf
             continue
 
@@ -147,8 +251,14 @@ def main():
             step[0] += 1
             comm.allreduce_adamw(0, 1, 2, 3, 0, ne, K.adamw_args(1e-5, 0.9, 0.999, 1e-8, 0.01, step[0], scale),
                                  max_blocks=a.max_blocks)
+        comm.multicast(0)
         t = timed(fused)
         row["fused_ms"], row["fused_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        if mc_avail:
+            comm.multicast(1)
+            t = timed(fused)
+            row["fused_mc_ms"], row["fused_mc_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
+        comm.multicast(-1)
         pl, ml, vl = (torch.zeros(ne, dtype=torch.bfloat16, device=dev) for _ in range(3))
 
         def unfused():
@@ -160,8 +270,10 @@ def main():
         results["rows"].append(row)
         if rank == 0:
             print(f"{nbytes >> 20:6d} MiB  p2p {row['p2p_ms']:8.3f} ms {row['p2p_busbw']:7.1f} GB/s | "
-                  f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s | fused AR+AdamW {row['fused_ms']:8.3f} ms | "
-                  f"nccl+adamw {row['nccl_plus_adamw_ms']:8.3f} ms", flush=True)
+                  + (f"multimem {row['mc_ms']:8.3f} ms {row['mc_busbw']:7.1f} GB/s ({row['mc_best_blocks']} CTAs) | " if mc_avail else "")
+                  + f"nccl {row['nccl_ms']:8.3f} ms {row['nccl_busbw']:7.1f} GB/s | fused AR+AdamW {row['fused_ms']:8.3f} ms | "
+                  + (f"fused multimem {row['fused_mc_ms']:8.3f} ms | " if mc_avail else "")
+                  + f"nccl+adamw {row['nccl_plus_adamw_ms']:8.3f} ms", flush=True)
         del buf, pl, ml, vl
     assert not comm.timed_out()
     if rank == 0 and a.json:

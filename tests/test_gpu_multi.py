@@ -17,8 +17,8 @@ def _need(n):
         pytest.skip(f"needs {n} GPUs")
 
 
-def _launch(tmp, name, steps, world, extra=()):
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1", PR_COMM_TIMEOUT_S="30")
+def _launch(tmp, name, steps, world, extra=(), env_extra=None):
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", PR_COMM_TIMEOUT_S="30", **(env_extra or {}))
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
            "--master-addr", "127.0.0.1", "--master-port", str(29800 + (os.getpid() % 100)),
            str(ROOT / "train.py"), "--distributed", "--synthetic-data", "--model-preset", "tiny", "--sequence-length", "256",
@@ -54,6 +54,32 @@ def test_two_gpu_train_resume_weight_equality(tmp_path, mode, sharded):
             a = (tmp_path / "straight" / "ckpt_20" / f"shard_{r:05d}.bin").read_bytes()
             b = (tmp_path / "resumed" / "ckpt_20" / f"shard_{r:05d}.bin").read_bytes()
             assert a == b, f"shard {r} differs"
+
+
+@pytest.mark.parametrize("mode", ["replicated", "fused"])
+def test_two_gpu_multicast_train_resume_weight_equality(tmp_path, mode):
+    """The same experiment with the NVSwitch multicast kernels forced on at W = 2
+    (PR_COMM_MULTICAST=1; a box without multicast support runs the P2P kernels instead and the
+    test still holds): the in-switch sum is deterministic, so straight and resumed runs end with
+    identical weights; and the multicast run stays within bf16 rounding of the P2P run."""
+    _need(2)
+    extra = ("--grad-sync", mode)
+    mc = {"PR_COMM_MULTICAST": "1"}
+    _launch(tmp_path, "straight", 20, 2, extra, mc)
+    _launch(tmp_path, "resumed", 10, 2, extra, mc)
+    _launch(tmp_path, "resumed", 20, 2, extra + ("--resume-from-checkpoint", "latest"), mc)
+    _launch(tmp_path, "p2p", 20, 2, extra, {"PR_COMM_MULTICAST": "0"})
+    A = torch.load(tmp_path / "straight" / "ckpt_20.pt", map_location="cpu")
+    B = torch.load(tmp_path / "resumed" / "ckpt_20.pt", map_location="cpu")
+    C = torch.load(tmp_path / "p2p" / "ckpt_20.pt", map_location="cpu")
+    for k in A["model"]:
+        assert torch.equal(A["model"][k], B["model"][k]), k
+        # 20 AdamW steps at lr 1e-3 move a weight by at most ~2e-2; the two exchanges differ by one
+        # bf16 ulp of a gradient per step, far below that
+        assert float((A["model"][k].float() - C["model"][k].float()).abs().max()) < 5e-2, k
+    for i in A["optimizer"]["state"]:
+        assert torch.equal(A["optimizer"]["state"][i]["exp_avg"], B["optimizer"]["state"][i]["exp_avg"])
+        assert torch.equal(A["optimizer"]["state"][i]["exp_avg_sq"], B["optimizer"]["state"][i]["exp_avg_sq"])
 
 
 def test_two_gpu_matches_vanilla_and_sharded(tmp_path):
