@@ -33,7 +33,11 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 METRIC = "tokens/s"
-WORKLOAD = "~1B model.py transformer (dim 2048, 16 layers, vocab 32768), bf16, seq 2048, batch 1/GPU, fused AdamW [BASELINE configs[1]]"
+WORKLOADS = {
+    "1b": "~1B model.py transformer (dim 2048, 16 layers, vocab 32768), bf16, seq 2048, batch 1/GPU, fused AdamW [BASELINE configs[1]]",
+    "8b": "default model.py transformer (dim 4096, 32 layers, vocab 131072, ~8B params), bf16, seq 2048, batch 1/GPU, fused AdamW [BASELINE configs[2]]",
+    "tiny": "tiny model.py transformer (dim 256, 4 layers, vocab 1024), bf16, batch 1/GPU, fused AdamW [BASELINE configs[0] shape, on the GPU path]",
+}
 
 
 def parse():
@@ -118,7 +122,7 @@ def run_reference(a):
         "impl": "reference", "metric": METRIC, "value": res["tokens_per_s"], "unit": "tokens/s", "n_gpus": a.gpus,
         "steps": res["steps"], "warmup": max(1, min(a.warmup, 2)), "ms_per_step": res["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "device": "host CPU", "note": "reference's CPU path restated call for call "
+        "config": {"workload": WORKLOADS[a.preset], "device": "host CPU", "note": "reference's CPU path restated call for call "
                    "(oracle/cpu_reference_port.py): torch fwd/bwd + torch.optim.AdamW(fused=True) on a bounded token sample"},
         "cpu_baseline": {"value": res["tokens_per_s"], "unit": "tokens/s", "cores": res["cores"], "kind": "port",
                          "sample": res["sample"]},
@@ -217,9 +221,11 @@ def run_b200(a):
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    t_issue0 = time.perf_counter()
     for s in range(a.warmup, total):
         trainer.step(*dev_batches[s])
         maybe_ckpt(s, "dev")
+    host_issue_ms = (time.perf_counter() - t_issue0) * 1e3 / a.steps      # host time to ENQUEUE a step
     e1.record()
     barrier()
     if a.profile_range:
@@ -333,13 +339,14 @@ def run_b200(a):
             "metric": METRIC, "value": tokens_per_step * a.steps / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "params": n_params, "global_batch": world, "seq_len": a.seq,
+            "config": {"workload": WORKLOADS[a.preset], "params": n_params, "global_batch": world, "seq_len": a.seq,
                        "parallelism": f"dp{world}", "grad_sync": a.grad_sync if world > 1 else "none (N=1)",
-                       "l2": "inputs >> L2: four 2 GB arenas streamed once per step",
+                       "l2": f"inputs >> L2: four {opt.arenas[0].layout.nbytes / 1e9:.1f} GB arenas streamed once per step",
                        "checkpoint": "none" if ckpt_at is None else f"1 {fmt} snapshot inside each timed region (staged pack on a side stream, D2H + file write in the writer thread)"},
             "e2e": {"value": tokens_per_step * a.steps / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / a.steps, "last_loss": loss_val},
             "gpu_launches": launches_timed,
+            "host_issue_ms_per_step": host_issue_ms,     # close to ms_per_step = the loop is launch-bound on the host
             "clocks": clocks.summary(),
             "roofline": {"kernel": "allreduce_adamw_kernel<W> (K1+K2 fused)" if fused_multi else "adamw_bf16_kernel<0,false> (K2)",
                          "bound": "hbm", "achieved": achieved, "peak": hbm_peak,

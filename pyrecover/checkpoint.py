@@ -313,7 +313,10 @@ def load_ckpt_distributed(
         if not _is_b200(optimizer):
             raise RuntimeError(f"{checkpoint_path} is a pyrecover_b200 sharded checkpoint; it loads into a "
                                "B200AdamW optimizer on a CUDA device")
-        small = _snapshotter(model, optimizer).load_sharded(checkpoint_path, verify)
+        world = dist.get_world_size() if is_distributed else 1
+        small = _snapshotter(model, optimizer).load_sharded(
+            checkpoint_path, verify, rank=dist.get_rank() if is_distributed else 0, world=world,
+            grad_sync=getattr(optimizer, "_grad_sync", None))
         for g, saved in zip(optimizer.param_groups, small["param_groups"]):
             g.update(saved)
         for gi, s in enumerate(small["opt_steps"]):

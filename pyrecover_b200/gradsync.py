@@ -112,8 +112,12 @@ class GradSync:
         for bi, b in enumerate(self._buckets):
             for idx in b["members"]:
                 self._bucket_of[idx] = bi
-        for q, gv, slot in zip(arena.params, arena.g_views, slots):
-            self._hooks.append(q.register_post_accumulate_grad_hook(self._make_hook(slot.index, gv)))
+        if self.overlap:
+            for q, gv, slot in zip(arena.params, arena.g_views, slots):
+                self._hooks.append(q.register_post_accumulate_grad_hook(self._make_hook(slot.index, gv)))
+        # without overlap nothing has to happen DURING backward: optimizer.step() gathers all
+        # gradients into the arena with one multi-tensor copy (147 python hook calls per step cost
+        # ~4 ms of host time, which a launch-bound loop cannot hide)
 
     def _make_hook(self, index: int, gview: torch.Tensor):
         def hook(param: torch.nn.Parameter):
@@ -151,6 +155,18 @@ class GradSync:
 
     # ---- called by B200AdamW.step() ---------------------------------------------------------
     def grads_ready(self) -> bool:
+        if not self.overlap:
+            grads = [q.grad for q in self.arena.params]
+            have = sum(g is not None for g in grads)
+            if have == 0:
+                return False
+            if have != len(grads):
+                raise RuntimeError(f"GradSync: {have} of {len(grads)} gradients arrived "
+                                   "(reference semantics: find_unused_parameters=False)")
+            torch._foreach_copy_(self.arena.g_views, grads)
+            for q in self.arena.params:
+                q.grad = None
+            return True
         if self._seen == 0:
             return False
         if self._seen != len(self.arena.params):
@@ -226,6 +242,24 @@ class GradSync:
                 self.comm.allgather_slices(REGION_M, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
                 self.comm.allgather_slices(REGION_V, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
             self._moments_replicated = True
+
+    def allgather_arena(self, name: str, t: torch.Tensor) -> None:
+        """Every rank holds its `slice_range()` of the flat arena tensor `t` (p, m or v); make every
+        rank hold all of it.  Symmetric arenas are gathered in place by K1's all-gather kernel;
+        a plain tensor (replicated mode keeps p / m / v outside the communicator) bounces through
+        the gradient arena, whose contents are dead outside backward."""
+        if self.world == 1:
+            return
+        arena = self.arena
+        nbytes = arena.layout.nbytes
+        symmetric = name == "g" or self.mode in ("fused", "overlap")
+        if symmetric:
+            self.comm.allgather_slices(_REGION[name], 0, nbytes, max_blocks=self.max_blocks)
+            return
+        lo, hi = self.slice_range()
+        arena.g[lo:hi].copy_(t[lo:hi])
+        self.comm.allgather_slices(REGION_G, 0, nbytes, max_blocks=self.max_blocks)
+        t.copy_(arena.g)
 
     def moments_loaded(self) -> None:
         self._moments_replicated = True

@@ -400,11 +400,7 @@ class Snapshotter:
             e_copied.synchronize()
             t2 = time.perf_counter()
             shard_path = d / f"shard_{rank:05d}.bin"
-            with open(str(shard_path) + ".tmp", "wb", buffering=0) as f:
-                for chunk in img.drain(self.side):
-                    f.write(chunk)
-                os.fsync(f.fileno())
-            os.replace(str(shard_path) + ".tmp", str(shard_path))
+            PT.write_raw(str(shard_path), img.drain(self.side))
             A, B = img.checksum()
             side = {"format": SHARD_FORMAT, "rank": rank, "world": world, "sum64": [A, B],
                     "image_bytes": img.image_bytes, "full_image_bytes": self.full_bytes,
@@ -424,21 +420,31 @@ class Snapshotter:
         if blocking:
             self.wait()
 
-    def load_sharded(self, dirpath: str, verify: bool = True) -> Dict[str, Any]:
-        """Read every shard of the directory (any saving world size) into the full pinned image,
-        upload, unpack into the live tensors, and verify each shard's PR-SUM64 on the GPU plus
-        that the shard sums add up to the image's.  Returns meta.pt's dict."""
+    def load_sharded(self, dirpath: str, verify: bool = True, rank: int = 0, world: int = 1,
+                     grad_sync=None) -> Dict[str, Any]:
+        """Restore from a sharded directory and return meta.pt's dict.
+
+        Same world size as the save and a GradSync at hand (the usual requeue): every rank reads
+        ONLY its own shard (1/W of the bytes) -> pinned -> H2D -> unpack + PR-SUM64 on the GPU, and
+        the slices are re-replicated over NVLink by K1's all-gather -- instead of the reference's W
+        full reads staggered by 3 s x rank (pyrecover/checkpoint.py:140-141, :352-356).
+        Any other world size: read every shard into the full pinned image, upload, unpack, verify
+        each shard's PR-SUM64."""
         self.wait()
         d = Path(dirpath)
         sides = sorted(d.glob("shard_*.json"))
         if not sides:
             raise RuntimeError(f"No checkpoint shards found in {d}")
         infos = [json.loads(s.read_text()) for s in sides]
-        world = infos[0]["world"]
-        if len(infos) != world or any(not (d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos):
-            raise RuntimeError(f"Sharded checkpoint {d} is incomplete ({len(infos)} of {world} shards)")
+        saved_world = infos[0]["world"]
+        if len(infos) != saved_world or any(not (d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos):
+            raise RuntimeError(f"Sharded checkpoint {d} is incomplete ({len(infos)} of {saved_world} shards)")
         if infos[0]["full_image_bytes"] != self.full_bytes:
             raise RuntimeError("checkpoint image layout differs from the live model")
+        if grad_sync is not None and world > 1 and saved_world == world and grad_sync.world == world \
+                and os.environ.get("PYRECOVER_B200_SLICE_LOAD", "1") != "0":
+            self._load_own_shard(d, next(i for i in infos if i["rank"] == rank), rank, world, grad_sync, verify)
+            return torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
         img = self.full()
         mv = img.host.view()
         for info in infos:
@@ -456,6 +462,26 @@ class Snapshotter:
                 if K._sum_to_ints(s) != tuple(info["sum64"]):
                     raise RuntimeError(f"Checksum mismatch for shard {info['rank']} of {d}")
         return torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
+
+    def _load_own_shard(self, d: Path, info: Dict[str, Any], rank: int, world: int, grad_sync, verify: bool) -> None:
+        import torch.distributed as dist
+        img = self.shard(rank, world)
+        if info["image_bytes"] != img.image_bytes or \
+                [list(x) for x in info["pieces"]] != [[p.global_off, p.nbytes, p.img_off] for p in img.pieces]:
+            raise RuntimeError(f"shard {rank} of {d} does not match this rank's slice layout")
+        with open(d / f"shard_{rank:05d}.bin", "rb", buffering=0) as f:
+            _read_exact(f, img.host.view(0, img.image_bytes), str(d))
+        got = img.restore()                        # H2D + unpack into the live slices + PR-SUM64
+        if verify and tuple(info["sum64"]) != got:
+            raise RuntimeError(f"Checksum mismatch for shard {rank} of {d}: stored {tuple(info['sum64'])}, "
+                               f"computed on GPU {got}")
+        for a in self.arenas:                      # slices -> every rank, over NVLink
+            for name, t in (("p", a.p), ("m", a.m), ("v", a.v)):
+                grad_sync.allgather_arena(name, t)
+        for t in self.extras:                      # stray tensors live in rank 0's shard
+            dist.broadcast(t, src=dist.get_global_rank(grad_sync.pg, 0) if grad_sync.pg is not None else 0,
+                           group=grad_sync.pg)
+        self.last_stats = {"load": "own shard + NVLink all-gather", "bytes_read": img.image_bytes}
 
     def close(self) -> None:
         self.wait()

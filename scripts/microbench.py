@@ -27,8 +27,77 @@ def timeit(fn, iters, warmup=3):
     return ts[len(ts) // 2], ts[0]
 
 
+def sweep(a, hbm):
+    """BASELINE configs[4], single-GPU legs: AdamW and checkpoint pack over buckets of 1 MB - 16 GB
+    (bf16 bucket bytes), torch's fused AdamW beside it.  Buckets whose working set fits the 126 MB
+    L2 are timed with an L2 flush (a 512 MB memset) before every launch."""
+    dev = "cuda"
+    flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+    rows = []
+    for lg in range(a.sweep_min_log2, a.sweep_max_log2 + 1):
+        nbytes = 1 << lg
+        n = nbytes // 2
+        p = (torch.randn(n, device=dev) * 0.02).bfloat16()
+        g = (torch.randn(n, device=dev) * 1e-3).bfloat16()
+        m, v = torch.zeros_like(p), torch.zeros_like(p)
+        need_flush = 4 * nbytes < (512 << 20)
+
+        def t(fn, iters=a.iters):
+            for _ in range(3):
+                fn()
+            ts = []
+            for _ in range(iters):
+                if need_flush:
+                    flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record()
+                torch.cuda.synchronize()
+                ts.append(e0.elapsed_time(e1))
+            ts.sort()
+            return ts[len(ts) // 2]
+        step = [0]
+
+        def k2():
+            step[0] += 1
+            K.adamw_(p, g, m, v, lr=1e-5, step=step[0], numerics=0)
+        row = {"bucket_bytes": nbytes, "l2_flushed": need_flush}
+        ms = t(k2)
+        row["adamw_ms"], row["adamw_gbs"] = ms, 14 * n / ms / 1e6
+        P = torch.nn.Parameter(p)
+        P.grad = g
+        opt = torch.optim.AdamW([P], lr=1e-5, fused=True)
+        ms = t(opt.step)
+        row["torch_fused_adamw_ms"], row["torch_fused_adamw_gbs"] = ms, 14 * n / ms / 1e6
+        del opt, P
+        if lg <= a.sweep_pack_max_log2:
+            s = torch.zeros(2, dtype=torch.int64, device=dev)
+            image = torch.zeros(3 * nbytes, dtype=torch.uint8, device=dev)
+            plan = K.PackPlan([p, m, v], [0, nbytes, 2 * nbytes], 3 * nbytes)
+            ms = t(lambda: plan.pack(image.data_ptr(), s))
+            row["pack_ms"], row["pack_gbs"] = ms, 2 * 3 * nbytes / ms / 1e6
+            ms = t(lambda: K.checksum_into(p, s))
+            row["checksum_ms"], row["checksum_gbs"] = ms, nbytes / ms / 1e6
+            plan.close()
+            del image
+        for k in ("adamw_gbs", "torch_fused_adamw_gbs", "pack_gbs", "checksum_gbs"):
+            if k in row:
+                row[k.replace("_gbs", "_frac")] = row[k] / hbm
+        rows.append(row)
+        print(f"{nbytes >> 20:6d} MiB bucket | AdamW {row['adamw_ms']:9.4f} ms {row['adamw_gbs']:7.0f} GB/s ({row['adamw_frac']:.2f}) | "
+              f"torch fused {row['torch_fused_adamw_ms']:9.4f} ms {row['torch_fused_adamw_gbs']:7.0f} GB/s | "
+              + (f"pack {row['pack_ms']:9.4f} ms {row['pack_gbs']:7.0f} GB/s ({row['pack_frac']:.2f}) | checksum {row['checksum_gbs']:7.0f} GB/s"
+                 if "pack_ms" in row else "pack: skipped (image would not fit)"), flush=True)
+        del p, g, m, v
+        torch.cuda.empty_cache()
+    return rows
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--sweep", action="store_true", help="bucket sweep 1 MB - 16 GB instead of the single-size table")
+    ap.add_argument("--sweep-min-log2", type=int, default=20)
+    ap.add_argument("--sweep-max-log2", type=int, default=34)
+    ap.add_argument("--sweep-pack-max-log2", type=int, default=33)
     ap.add_argument("--n-log2", type=int, default=30)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--json", type=str, default=None)
@@ -40,6 +109,12 @@ def main():
         peaks = json.loads(pk.read_text())
     hbm = peaks.get("hbm_gbs", 6650.0)
     res = {"n": n, "hbm_peak_gbs": hbm, "device": torch.cuda.get_device_name()}
+    if a.sweep:
+        res = {"hbm_peak_gbs": hbm, "device": torch.cuda.get_device_name(), "rows": sweep(a, hbm)}
+        if a.json:
+            Path(a.json).parent.mkdir(parents=True, exist_ok=True)
+            Path(a.json).write_text(json.dumps(res, indent=1))
+        return
     dev = "cuda"
     p = (torch.randn(n, device=dev) * 0.02).bfloat16()
     g = (torch.randn(n, device=dev) * 1e-3).bfloat16()

@@ -191,6 +191,57 @@ def test_archive_writer_is_torch_loadable_and_aligned(tmp_path):
     assert zipfile.ZipFile(path).testzip() is None
 
 
+@pytest.mark.parametrize("zip64", [False, True])
+def test_archive_writer_streams_big_records_direct_and_zip64(tmp_path, monkeypatch, zip64):
+    """The streamed-record path: page-aligned buffers go out with O_DIRECT where the filesystem
+    takes it (buffered otherwise -- same bytes either way), the CRC comes from the helper thread,
+    the md5 is that of the finished file, and the zip64 framing (forced here with a small limit;
+    real checkpoints cross 2 GiB) is accepted by torch.load and by the zipfile module."""
+    import mmap
+    import zipfile
+    from collections import OrderedDict
+
+    from pyrecover_b200 import ptfile as PT
+    if zip64:
+        monkeypatch.setattr(PT, "_ZIP64_LIMIT", (1 << 20) - 1)
+    chunk = 1 << 20
+    bufs = []
+    for i in range(3):
+        m = mmap.mmap(-1, chunk)                      # page aligned, like the pinned arena
+        m.write(np.random.default_rng(i).integers(0, 256, chunk, dtype=np.uint8).tobytes())
+        bufs.append(m)
+    tail = 4096 + 320                                 # last chunk: one aligned block + an unaligned rest
+    total = 2 * chunk + tail
+    parts = [memoryview(bufs[0]), memoryview(bufs[1]), memoryview(bufs[2])[:tail]]
+    want = b"".join(bytes(x) for x in parts)
+    rec = PT.RecordRef("0", torch.uint8, total)
+    state = {"step": 3, "model": OrderedDict(head=PT.TensorStub(rec, 7, (100,)), tail=PT.TensorStub(rec, total - 50, (50,)))}
+    out = {}
+    for direct in (None, False):
+        (tmp_path / str(direct)).mkdir()
+        path = tmp_path / str(direct) / "big.pt"
+        info = PT.write_archive(str(path), PT.dumps_state(state), [("0", (total, iter(parts)))], md5=True, direct=direct)
+        raw = path.read_bytes()
+        out[direct] = raw
+        assert info["md5"] == hashlib.md5(raw).hexdigest() and info["bytes"] == len(raw)
+        assert info["offsets"]["0"] % 4096 == 0
+        assert raw[info["offsets"]["0"]:info["offsets"]["0"] + total] == want
+        assert zipfile.ZipFile(path).testzip() is None
+        for kw in ({"weights_only": True}, {"mmap": True}):
+            ck = torch.load(path, map_location="cpu", **kw)
+            assert bytes(ck["model"]["head"].numpy().tobytes()) == want[7:107]
+            assert bytes(ck["model"]["tail"].numpy().tobytes()) == want[-50:]
+        assert PT.record_offsets(str(path))["data/0"] == (info["offsets"]["0"], total)
+    assert out[None] == out[False]
+    # a short stream is an error and leaves nothing behind
+    with pytest.raises(IOError):
+        PT.write_archive(str(tmp_path / "short.pt"), PT.dumps_state(state), [("0", (total, iter(parts[:2])))])
+    assert not (tmp_path / "short.pt").exists() and not (tmp_path / "short.pt.tmp").exists()
+    # raw shard writer
+    n = PT.write_raw(str(tmp_path / "shard.bin"), iter(parts))
+    assert n == total and (tmp_path / "shard.bin").read_bytes() == want
+
+
 def test_flat_layout_alignment_and_slices():
     from pyrecover_b200.flat import FlatLayout
     shapes = [torch.Size(s) for s in [(1024, 256), (128, 256), (256,), (7, 3)]]
