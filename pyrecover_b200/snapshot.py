@@ -570,5 +570,33 @@ def rotate_dirs(base: Path, max_keep: int) -> None:
         return
     import shutil
     dirs = sorted((x for x in base.glob("ckpt_*") if x.is_dir()), key=_step_key)
+    now = time.time()
     for x in dirs[:-max_keep] if len(dirs) > max_keep else []:
+        # ranks are only loosely in step while their writer threads run: never pull a directory
+        # from under a peer that is still writing its shard (incomplete and recently touched)
+        if _sharded_dir_in_progress(x, now):
+            continue
         shutil.rmtree(x, ignore_errors=True)
+
+
+def _sharded_dir_in_progress(d: Path, now: float, grace_s: float = 900.0) -> bool:
+    sides = list(d.glob("shard_*.json")) + list(d.glob("shard_*.bin.tmp")) + list(d.glob("shard_*.bin"))
+    if not sides and not (d / ".metadata").exists():
+        try:
+            return now - d.stat().st_mtime < grace_s          # just created, nothing written yet
+        except OSError:
+            return False
+    marks = list(d.glob("COMPLETE_*"))
+    if marks:
+        try:
+            if len(marks) >= int(marks[0].read_text()):
+                return False                                   # complete
+        except (ValueError, OSError):
+            pass
+    elif (d / ".metadata").exists():
+        return False                                           # a torch.distributed.checkpoint directory
+    try:
+        newest = max(f.stat().st_mtime for f in d.iterdir())
+    except (OSError, ValueError):
+        return False
+    return now - newest < grace_s

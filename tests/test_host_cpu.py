@@ -155,10 +155,25 @@ def test_rotation_is_by_step_number_and_scoped(tmp_path):
     rotate_files(tmp_path, 0)
     assert len(list(tmp_path.glob("*.pt"))) == 2
     for s in (5, 10, 15):
-        (tmp_path / f"ckpt_{s}").mkdir()
+        d = tmp_path / f"ckpt_{s}"
+        d.mkdir()
+        (d / "shard_00000.bin").write_bytes(b"x")
+        (d / "shard_00000.json").write_text("{}")
+        (d / "COMPLETE_00000").write_text("1")
     (tmp_path / "logs").mkdir()
+    # a directory a slower rank is still writing (2 ranks, one marker) is never pulled from under it
+    busy = tmp_path / "ckpt_7"
+    busy.mkdir()
+    (busy / "shard_00001.bin.tmp").write_bytes(b"x")
+    (busy / "COMPLETE_00000").write_text("2")
     rotate_dirs(tmp_path, 1)
     assert (tmp_path / "logs").exists() and (tmp_path / "ckpt_15").exists() and not (tmp_path / "ckpt_5").exists()
+    assert not (tmp_path / "ckpt_10").exists() and busy.exists()
+    old = time.time() - 3600                          # ... unless it has been dead for a long time
+    for f in busy.iterdir():
+        os.utime(f, (old, old))
+    rotate_dirs(tmp_path, 1)
+    assert not busy.exists()
 
 
 # ------------------------------------------------------------------------- archive --------
