@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define PR_ABI_VERSION 1
+#define PR_ABI_VERSION 2
 #define PR_MAX_WORLD 8            /* one NVSwitch domain: 8 x B200                          */
 #define PR_MAX_REGIONS 4          /* symmetric regions per communicator                     */
 #define PR_EXPORT_BLOB_BYTES 512  /* bytes pr_comm_export writes per rank                   */
@@ -67,6 +67,9 @@ typedef struct pr_adamw_args {
     int64_t step;
     int32_t numerics;
     int32_t grad_dtype;  /* pr_dtype of g */
+    const float *grad_scale_dev;  /* optional DEVICE scalar multiplied (in binary32) into grad_scale when the
+                                     kernel starts -- the clip coefficient pr_grad_norm leaves on the device,
+                                     so clipping costs no host synchronisation.  NULL = none. */
 } pr_adamw_args;
 
 int pr_adamw(void *p_dev, const void *g_dev, void *m_dev, void *v_dev, uint64_t n,
@@ -84,6 +87,26 @@ int pr_adamw_plan_create(const uint64_t *elem_off, const uint64_t *numel, int n_
 int pr_adamw_plan_destroy(pr_adamw_plan *plan);
 int pr_adamw_scattered(const pr_adamw_plan *plan, void *p_dev, const void *const *grad_dev,
                        void *m_dev, void *v_dev, const pr_adamw_args *args, void *stream);
+
+/* Global-norm gradient clipping -- the reference's clip_grad_norm_ (utils.py:84-89: total =
+ * get_total_norm(grads), then clip_grads_with_norm_(params, max_norm, total)), whose call is
+ * commented out at train.py:271-272 with the flag --grad-max-norm (utils.py:171-175) left behind.
+ *   out_dev[0] = prescale * sqrt(sum g_i^2)                    (the total L2 norm)
+ *   out_dev[1] = min(1, max_norm / (out_dev[0] + 1e-6))        (1 when max_norm <= 0)
+ *   out_dev[2] = 1 if the norm is not finite, else 0           (the reference raises; check it lazily)
+ * Pass out_dev + 1 as pr_adamw_args.grad_scale_dev and the update applies the coefficient in
+ * fp32 inside K2 -- no extra pass over the gradients and no rounding of the clipped gradients to
+ * bf16 as clip_grads_with_norm_ does.  Two launches; squares are summed in fp32 per thread, in
+ * double across threads and CTAs, in a fixed order: the result is deterministic for a given n
+ * and GPU (bit-exact resume depends on it).  scratch_dev: >= PR_GRAD_NORM_SCRATCH doubles owned
+ * by the caller (no allocation happens here).
+ * pr_grad_norm_scattered reads every tensor's gradient where autograd left it (see
+ * pr_adamw_scattered). */
+#define PR_GRAD_NORM_SCRATCH 2048
+int pr_grad_norm(const void *g_dev, uint64_t n, int dtype, float prescale, float max_norm,
+                 float *out_dev, double *scratch_dev, void *stream);
+int pr_grad_norm_scattered(const pr_adamw_plan *plan, const void *const *grad_dev, float prescale,
+                           float max_norm, float *out_dev, double *scratch_dev, void *stream);
 
 /* ---------------------------------------------------------------- K3: checkpoint -----
  * PR-SUM64, the on-GPU checksum that stands in for hashlib.md5 over the file -- reference

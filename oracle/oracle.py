@@ -53,7 +53,10 @@ def lib() -> ctypes.CDLL:
         L.orc_checksum64.argtypes = [vp, sz, u64, vp]
         L.orc_pack.argtypes = [vp, vp, vp, ctypes.c_int, vp, u64, vp]
         L.orc_unpack.argtypes = [vp, vp, vp, ctypes.c_int, vp]
-        for f in ("orc_adamw_prepare", "orc_adamw_bf16", "orc_adamw_f32", "orc_adamw_bf16_gf32",
+        L.orc_grad_norm_bf16.argtypes = [vp, sz, ctypes.c_float, ctypes.c_float, vp]
+        L.orc_grad_norm_f32.argtypes = [vp, sz, ctypes.c_float, ctypes.c_float, vp]
+        L.orc_scale_mul.argtypes = [cp, ctypes.c_float]
+        for f in ("orc_grad_norm_bf16", "orc_grad_norm_f32", "orc_scale_mul", "orc_adamw_prepare", "orc_adamw_bf16", "orc_adamw_f32", "orc_adamw_bf16_gf32",
                   "orc_allreduce_bf16", "orc_allreduce_bf16_to_f32", "orc_allreduce_bf16_ddp",
                   "orc_allreduce_f32", "orc_checksum64", "orc_pack", "orc_unpack"):
             getattr(L, f).restype = None
@@ -86,19 +89,36 @@ def _ptr(a: np.ndarray) -> ctypes.c_void_p:
     return ctypes.c_void_p(a.ctypes.data)
 
 
-def adamw_consts(lr, beta1, beta2, eps, wd, step, gscale=1.0) -> AdamWConsts:
+def adamw_consts(lr, beta1, beta2, eps, wd, step, gscale=1.0, coef=None) -> AdamWConsts:
+    """coef: clip coefficient (binary32) multiplied into the gradient scale, as K2 does with
+    pr_adamw_args.grad_scale_dev."""
     c = AdamWConsts()
     lib().orc_adamw_prepare(lr, beta1, beta2, eps, wd, int(step), gscale, ctypes.byref(c))
+    if coef is not None:
+        lib().orc_scale_mul(ctypes.byref(c), float(coef))
     return c
+
+
+def grad_norm(g: np.ndarray, max_norm: float, prescale: float = 1.0):
+    """(norm, coefficient, nonfinite) of a flat gradient array (uint16 bf16 bits or float32) --
+    reference utils.py:84-89 (clip_grad_norm_)."""
+    out = np.zeros(3, dtype=np.float32)
+    g = np.ascontiguousarray(g)
+    if g.dtype == np.uint16:
+        lib().orc_grad_norm_bf16(_ptr(g), g.size, prescale, max_norm, _ptr(out))
+    else:
+        assert g.dtype == np.float32
+        lib().orc_grad_norm_f32(_ptr(g), g.size, prescale, max_norm, _ptr(out))
+    return float(out[0]), float(out[1]), bool(out[2])
 
 
 # --------------------------------------------------------------------------- AdamW ------
 
 def adamw_bf16(p, g, m, v, *, lr, beta1=0.9, beta2=0.999, eps=1e-8, wd=0.01, step=1,
-               gscale=1.0, mode=0):
+               gscale=1.0, mode=0, coef=None):
     """In-place on uint16 arrays p, m, v.  mode 0 = fp32 op-math (fused class),
     mode 1 = bf16 rounding after every torch op (_single_tensor_adam class)."""
-    c = adamw_consts(lr, beta1, beta2, eps, wd, step, gscale)
+    c = adamw_consts(lr, beta1, beta2, eps, wd, step, gscale, coef)
     for a in (p, g, m, v):
         assert a.dtype == np.uint16 and a.size == p.size
     lib().orc_adamw_bf16(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.size, ctypes.byref(c), mode)

@@ -235,3 +235,50 @@ void orc_unpack(const void *packed, const uint64_t *nbytes, const uint64_t *src_
                 void *const *dst) {
     for (int s = 0; s < n; ++s) memcpy(dst[s], (const uint8_t *)packed + src_off[s], (size_t)nbytes[s]);
 }
+
+/* ---------------------------------------------------------------------------------------
+ * Global-norm clipping -- reference utils.py:84-89:
+ *     total = torch.nn.utils.get_total_norm(grads, error_if_nonfinite=True)      (L2 over all grads)
+ *     torch.nn.utils.clip_grads_with_norm_(params, max_norm, total)
+ * whose arithmetic (torch/nn/utils/clip_grad.py) is coef = max_norm / (total + 1e-6), clamped to
+ * at most 1, and g *= coef.  The sum of squares is taken in double here (torch accumulates in the
+ * gradient dtype's op-math; the pins in tests/ state the tolerance); the coefficient is formed in
+ * binary32 exactly as the CUDA kernel does, so that a given norm yields the same coefficient bits.
+ * out[0] = norm, out[1] = coefficient, out[2] = 1 if the norm is not finite.
+ * A coefficient is applied by multiplying it (in binary32) into the gradient scale:
+ * orc_scale_mul below is that one operation. */
+void orc_grad_norm_bf16(const bf16_t *g, size_t n, float prescale, float max_norm, float *out) {
+    double s = 0.0;
+    for (size_t i = 0; i < n; ++i) {
+        double x = (double)bf2f(g[i]);
+        s += x * x;
+    }
+    float norm = prescale * (float)sqrt(s);
+    int finite = isfinite(norm);
+    float coef = 1.0f;
+    if (max_norm > 0.0f && finite) {
+        coef = max_norm / (norm + 1e-6f);
+        if (coef > 1.0f) coef = 1.0f;
+    }
+    out[0] = norm;
+    out[1] = coef;
+    out[2] = finite ? 0.0f : 1.0f;
+}
+
+void orc_grad_norm_f32(const float *g, size_t n, float prescale, float max_norm, float *out) {
+    double s = 0.0;
+    for (size_t i = 0; i < n; ++i) s += (double)g[i] * (double)g[i];
+    float norm = prescale * (float)sqrt(s);
+    int finite = isfinite(norm);
+    float coef = 1.0f;
+    if (max_norm > 0.0f && finite) {
+        coef = max_norm / (norm + 1e-6f);
+        if (coef > 1.0f) coef = 1.0f;
+    }
+    out[0] = norm;
+    out[1] = coef;
+    out[2] = finite ? 0.0f : 1.0f;
+}
+
+/* gscale <- gscale * coef in binary32 (what resolve_gscale does on the device). */
+void orc_scale_mul(orc_adamw_consts *c, float coef) { c->gscale = c->gscale * coef; }

@@ -254,8 +254,6 @@ def save_ckpt_distributed(
         _save_barrier(fast)
     os.makedirs(os.path.dirname(str(checkpoint_path)) or ".", exist_ok=True)
     if fast:
-        if getattr(optimizer, "_grad_sync", None) is not None and optimizer._grad_sync.mode == "overlap":
-            optimizer._grad_sync.replicate_moments()      # per-bucket ownership -> arena slices
         world = dist.get_world_size() if is_distributed else 1
         groups = [{k: v for k, v in g.items() if k != "params"} for g in optimizer.param_groups]
         small = {"epoch": epoch, "step": step, "param_groups": groups,

@@ -15,6 +15,8 @@ LIB_PATH = PKG_DIR / "libpyrecover_b200.so"
 
 PR_BF16, PR_F32 = 0, 1
 PR_AR_AUTO, PR_AR_ONE_SHOT, PR_AR_TWO_SHOT, PR_AR_MULTIMEM = 0, 1, 2, 3
+PR_ABI_VERSION = 2
+PR_GRAD_NORM_SCRATCH = 2048
 PR_MAX_WORLD = 8
 PR_MAX_REGIONS = 4
 PR_EXPORT_BLOB_BYTES = 512
@@ -24,7 +26,7 @@ class AdamWArgs(ctypes.Structure):
     """struct pr_adamw_args"""
     _fields_ = [("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
                 ("weight_decay", c_double), ("grad_scale", c_double), ("step", c_int64),
-                ("numerics", c_int32), ("grad_dtype", c_int32)]
+                ("numerics", c_int32), ("grad_dtype", c_int32), ("grad_scale_dev", c_void_p)]
 
 
 _SIGNATURES = {
@@ -38,6 +40,8 @@ _SIGNATURES = {
     "pr_adamw_plan_create": (c_int, [c_void_p, c_void_p, c_int, c_uint64, POINTER(c_void_p)]),
     "pr_adamw_plan_destroy": (c_int, [c_void_p]),
     "pr_adamw_scattered": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(AdamWArgs), c_void_p]),
+    "pr_grad_norm": (c_int, [c_void_p, c_uint64, c_int, c_float, c_float, c_void_p, c_void_p, c_void_p]),
+    "pr_grad_norm_scattered": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "pr_checksum": (c_int, [c_void_p, c_uint64, c_uint64, c_void_p, c_void_p]),
     "pr_pack_plan_create": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_uint64, POINTER(c_void_p)]),
     "pr_pack_plan_destroy": (c_int, [c_void_p]),
@@ -95,7 +99,7 @@ def lib() -> ctypes.CDLL:
             fn = getattr(L, name)   # AttributeError here = header/library mismatch
             fn.restype = res
             fn.argtypes = args
-        if L.pr_abi_version() != 1:
+        if L.pr_abi_version() != PR_ABI_VERSION:
             raise RuntimeError(f"ABI version mismatch: library reports {L.pr_abi_version()}")
         _lib = L
     return _lib

@@ -43,7 +43,8 @@ __device__ __forceinline__ void update_vec8(uint4 &P, const float (&g)[8], uint4
 template <int NUMERICS, bool GRAD_F32>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
 adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__restrict__ m,
-                  uint4 *__restrict__ v, uint64_t nvec, AdamWConsts c) {
+                  uint4 *__restrict__ v, uint64_t nvec, AdamWConsts c_) {
+    const AdamWConsts c = resolve_gscale(c_);
     const AdamWFast f = make_adamw_fast(c);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
@@ -81,7 +82,8 @@ adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__r
 
 __global__ void __launch_bounds__(kThreads)
 adamw_f32_kernel(float4 *__restrict__ p, const float4 *__restrict__ g, float4 *__restrict__ m,
-                 float4 *__restrict__ v, uint64_t nvec, AdamWConsts c) {
+                 float4 *__restrict__ v, uint64_t nvec, AdamWConsts c_) {
+    const AdamWConsts c = resolve_gscale(c_);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     for (uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
         float4 P = p[i], G = __ldg(g + i), M = m[i], V = v[i];
@@ -96,7 +98,8 @@ adamw_f32_kernel(float4 *__restrict__ p, const float4 *__restrict__ g, float4 *_
 // Element-wise path for the < 1 vector tail and for arenas that are not 16-B aligned.
 template <int NUMERICS>
 __global__ void adamw_scalar_kernel(void *p_, const void *g_, void *m_, void *v_, uint64_t first,
-                                    uint64_t n, int dtype, int grad_dtype, AdamWConsts c) {
+                                    uint64_t n, int dtype, int grad_dtype, AdamWConsts c_) {
+    const AdamWConsts c = resolve_gscale(c_);
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         if (dtype == PR_F32) {
@@ -140,7 +143,8 @@ template <int NUMERICS>
 __global__ void __launch_bounds__(kThreads, kMinBlocks)
 adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, uint16_t *__restrict__ v,
                             AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
-                            const __grid_constant__ GradPtrs gp, AdamWConsts c) {
+                            const __grid_constant__ GradPtrs gp, AdamWConsts c_) {
+    const AdamWConsts c = resolve_gscale(c_);
     const AdamWFast f = make_adamw_fast(c);
     for (uint64_t t = tile_lo + blockIdx.x; t < tile_hi; t += gridDim.x) {
         const uint32_t s = pd.tile_seg[t];
@@ -182,6 +186,140 @@ adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, 
             if (NUMERICS == 1) adamw_stepwise_bf16(pf, g, mf, vf, c);
             else adamw_fp32(pf, g, mf, vf, c);
             p[i] = (uint16_t)f2bf_bits(pf); m[i] = (uint16_t)f2bf_bits(mf); v[i] = (uint16_t)f2bf_bits(vf);
+        }
+    }
+}
+
+// ---- global gradient norm (clip_grad_norm_, reference utils.py:84-89) -------------------------
+// Roofline: HBM, 2 B per bf16 gradient element read once.  Stage 1: fp32 sum of squares per
+// thread, double from the warp shuffle on; one double per CTA.  Stage 2: one CTA adds the CTA
+// partials in a fixed order and writes norm / clip coefficient / non-finite flag.
+constexpr int kNormThreads = 256;
+
+__device__ __forceinline__ float sumsq_vec(const uint4 &G, float s) {
+    const uint32_t *w = &G.x;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const float a = bf_lo(w[k]), b = bf_hi(w[k]);
+        s = __fmaf_rn(a, a, s);
+        s = __fmaf_rn(b, b, s);
+    }
+    return s;
+}
+
+__device__ __forceinline__ void block_partial(float s, double *partial) {
+    __shared__ double warp_sum[kNormThreads / 32];
+    double d = (double)s;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+    if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = d;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < kNormThreads / 32; ++w) t += warp_sum[w];
+        partial[blockIdx.x] = t;
+    }
+}
+
+template <bool F32>
+__global__ void __launch_bounds__(kNormThreads)
+sumsq_flat_kernel(const void *__restrict__ g_, uint64_t n, double *__restrict__ partial) {
+    const uint64_t stride = (uint64_t)gridDim.x * kNormThreads;
+    const uint64_t i0 = (uint64_t)blockIdx.x * kNormThreads + threadIdx.x;
+    float s = 0.0f;
+    const int per_vec = F32 ? 4 : 8;
+    const uint64_t nvec = n / per_vec;
+    const uint4 *G = reinterpret_cast<const uint4 *>(g_);
+    uint64_t i = i0;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {          // 4 independent 16-B loads in flight
+        uint4 a = ld_stream_nc(G + i), b = ld_stream_nc(G + i + stride), c = ld_stream_nc(G + i + 2 * stride),
+              d = ld_stream_nc(G + i + 3 * stride);
+        if (F32) {
+            const uint4 q[4] = {a, b, c, d};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                float x = __uint_as_float(q[k].x), y = __uint_as_float(q[k].y), z = __uint_as_float(q[k].z),
+                      w = __uint_as_float(q[k].w);
+                s = __fmaf_rn(x, x, s); s = __fmaf_rn(y, y, s); s = __fmaf_rn(z, z, s); s = __fmaf_rn(w, w, s);
+            }
+        } else {
+            s = sumsq_vec(a, s); s = sumsq_vec(b, s); s = sumsq_vec(c, s); s = sumsq_vec(d, s);
+        }
+    }
+    for (; i < nvec; i += stride) {
+        uint4 a = ld_stream_nc(G + i);
+        if (F32) {
+            float x = __uint_as_float(a.x), y = __uint_as_float(a.y), z = __uint_as_float(a.z), w = __uint_as_float(a.w);
+            s = __fmaf_rn(x, x, s); s = __fmaf_rn(y, y, s); s = __fmaf_rn(z, z, s); s = __fmaf_rn(w, w, s);
+        } else {
+            s = sumsq_vec(a, s);
+        }
+    }
+    for (uint64_t e = nvec * per_vec + i0; e < n; e += stride) {     // < 1 vector of tail elements
+        const float x = F32 ? reinterpret_cast<const float *>(g_)[e]
+                            : __uint_as_float((uint32_t)reinterpret_cast<const uint16_t *>(g_)[e] << 16);
+        s = __fmaf_rn(x, x, s);
+    }
+    block_partial(s, partial);
+}
+
+__global__ void __launch_bounds__(kNormThreads)
+sumsq_scattered_kernel(AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
+                       const __grid_constant__ GradPtrs gp, double *__restrict__ partial) {
+    float s = 0.0f;
+    for (uint64_t t = tile_lo + blockIdx.x; t < tile_hi; t += gridDim.x) {
+        const uint32_t seg = pd.tile_seg[t];
+        const uint64_t off = (t - pd.tile_first[seg]) * kTileElems;
+        const uint64_t left = pd.numel[seg] - off;
+        const uint32_t n = left < kTileElems ? (uint32_t)left : kTileElems;
+        const uint16_t *gs = reinterpret_cast<const uint16_t *>(gp.ptr[seg - seg_lo]) + off;
+        const uint4 *G = reinterpret_cast<const uint4 *>(gs);
+        const uint32_t nvec = n / 8;
+        uint32_t k = threadIdx.x;
+        for (; k + kNormThreads < nvec; k += 2 * kNormThreads) {
+            uint4 a = ld_stream_nc(G + k), b = ld_stream_nc(G + k + kNormThreads);
+            s = sumsq_vec(a, s);
+            s = sumsq_vec(b, s);
+        }
+        for (; k < nvec; k += kNormThreads) s = sumsq_vec(ld_stream_nc(G + k), s);
+        if (threadIdx.x < (n & 7u)) {
+            const float x = __uint_as_float((uint32_t)gs[8u * nvec + threadIdx.x] << 16);
+            s = __fmaf_rn(x, x, s);
+        }
+    }
+    block_partial(s, partial);
+}
+
+// partial[first .. first + count) -> out (norm, coefficient, non-finite flag).  `accumulate` adds to
+// the running sum kept in partial[PR_GRAD_NORM_SCRATCH - 1] instead of finishing (the scattered
+// variant launches once per group of kMaxGradPtrs tensors).
+__global__ void __launch_bounds__(kNormThreads)
+norm_finish_kernel(double *__restrict__ partial, int count, float prescale, float max_norm,
+                   float *__restrict__ out, int first_group, int last_group) {
+    __shared__ double sh[kNormThreads];
+    double t = 0.0;
+    for (int i = threadIdx.x; i < count; i += kNormThreads) t += partial[i];
+    sh[threadIdx.x] = t;
+    __syncthreads();
+    for (int o = kNormThreads / 2; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        double total = sh[0] + (first_group ? 0.0 : partial[PR_GRAD_NORM_SCRATCH - 1]);
+        partial[PR_GRAD_NORM_SCRATCH - 1] = total;
+        if (last_group) {
+            const float norm = __fmul_rn(prescale, (float)sqrt(total));
+            const bool finite = isfinite(norm);
+            float coef = 1.0f;
+            if (max_norm > 0.0f && finite) {
+                coef = __fdiv_rn(max_norm, __fadd_rn(norm, 1e-6f));
+                if (coef > 1.0f) coef = 1.0f;
+            }
+            out[0] = norm;
+            out[1] = coef;
+            out[2] = finite ? 0.0f : 1.0f;
         }
     }
 }
@@ -346,6 +484,49 @@ extern "C" int pr_adamw_scattered(const pr_adamw_plan *plan, void *p, const void
                                                                          plan->dev, t0, t1, (uint32_t)s0, gp, c);
         PR_CUDA(cudaGetLastError());
         pr_count_launch();
+    }
+    return PR_OK;
+}
+
+extern "C" int pr_grad_norm(const void *g, uint64_t n, int dtype, float prescale, float max_norm, float *out,
+                            double *scratch, void *stream_) {
+    PR_REQUIRE(out && scratch, "pr_grad_norm: NULL output or scratch");
+    PR_REQUIRE(dtype == PR_BF16 || dtype == PR_F32, "pr_grad_norm: dtype %d unsupported", dtype);
+    PR_REQUIRE(n == 0 || (g != nullptr && pr_aligned16(g)), "pr_grad_norm: gradient buffer is NULL or not 16-B aligned");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int per_vec = dtype == PR_F32 ? 4 : 8;
+    int grid = grid_for(n / per_vec + 1, kNormThreads * 4, 4);
+    if (grid > PR_GRAD_NORM_SCRATCH - 1) grid = PR_GRAD_NORM_SCRATCH - 1;
+    if (dtype == PR_F32) sumsq_flat_kernel<true><<<grid, kNormThreads, 0, stream>>>(g, n, scratch);
+    else sumsq_flat_kernel<false><<<grid, kNormThreads, 0, stream>>>(g, n, scratch);
+    PR_CUDA(cudaGetLastError());
+    norm_finish_kernel<<<1, kNormThreads, 0, stream>>>(scratch, grid, prescale, max_norm, out, 1, 1);
+    PR_CUDA(cudaGetLastError());
+    pr_count_launch(2);
+    return PR_OK;
+}
+
+extern "C" int pr_grad_norm_scattered(const pr_adamw_plan *plan, const void *const *grad_dev, float prescale,
+                                      float max_norm, float *out, double *scratch, void *stream_) {
+    PR_REQUIRE(plan && grad_dev && out && scratch, "pr_grad_norm_scattered: NULL argument");
+    for (int i = 0; i < plan->n; ++i)
+        PR_REQUIRE(grad_dev[i] != nullptr && pr_aligned16(grad_dev[i]),
+                   "pr_grad_norm_scattered: gradient %d is NULL or not 16-B aligned", i);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    for (int lo = 0; lo < plan->n; lo += kMaxGradPtrs) {
+        const int hi = lo + kMaxGradPtrs < plan->n ? lo + kMaxGradPtrs : plan->n;
+        GradPtrs gp;
+        memset(&gp, 0, sizeof(gp));
+        for (int i = lo; i < hi; ++i) gp.ptr[i - lo] = grad_dev[i];
+        const uint64_t t_lo = plan->tile_first[lo], t_hi = plan->tile_first[hi];
+        int grid = grid_for(t_hi - t_lo, 1, 4);
+        if (grid > PR_GRAD_NORM_SCRATCH - 1) grid = PR_GRAD_NORM_SCRATCH - 1;
+        sumsq_scattered_kernel<<<grid, kNormThreads, 0, stream>>>(plan->dev, t_lo, t_hi, (uint32_t)lo, gp, scratch);
+        PR_CUDA(cudaGetLastError());
+        norm_finish_kernel<<<1, kNormThreads, 0, stream>>>(scratch, grid, prescale, max_norm, out, lo == 0 ? 1 : 0,
+                                                           hi == plan->n ? 1 : 0);
+        PR_CUDA(cudaGetLastError());
+        pr_count_launch(2);
     }
     return PR_OK;
 }

@@ -50,7 +50,11 @@ namespace {
 constexpr int kThreads = 512;
 constexpr int kMaxBlocks = 512;          // flag words are provisioned for this many CTAs
 constexpr int kSlots = 2;
-constexpr int kMulticastBlocks = 64;     // default grid of the multicast kernels (tunable per call: max_blocks)
+// default grid of the multicast kernels (tunable per call: max_blocks).  The switch does the adding, so
+// a GPU only has to keep N/W of requests in flight: measured on 8 x B200, 16 CTAs are fastest up
+// to 512 MiB and 32 above (845.8 GB/s bus at 2 GiB); 148 CTAs are SLOWER (714 GB/s)
+constexpr int kMulticastBlocksSmall = 16, kMulticastBlocksLarge = 32;
+constexpr uint64_t kMulticastLargeBytes = 1ull << 30;
 constexpr int kOneShotVecPerThread = 4;  // register budget of the one-shot kernel
 constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * PR_MAX_WORLD;
 constexpr uint32_t kBlobMagic = 0x50523142u;  // "PR1B"
@@ -222,7 +226,8 @@ allreduce_oneshot_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
 // ---- fused reduce-scatter -> AdamW -> parameter all-gather (bf16) ----------------------------
 template <int W>
 __global__ void __launch_bounds__(kThreads, 1)
-allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac) {
+allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac_) {
+    const AdamWConsts ac = resolve_gscale(ac_);
     const int rank = my_rank(c);
     const uint64_t poff = goff;
     uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
@@ -331,7 +336,8 @@ allreduce_mc_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
 // fused: switch-reduced gradient slice -> AdamW on the local (p, m, v) slice -> multicast store of
 // the updated parameters into every rank's parameter region
 __global__ void __launch_bounds__(kThreads, 1)
-allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac) {
+allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac_) {
+    const AdamWConsts ac = resolve_gscale(ac_);
     const int rank = c.rank;
     const uint8_t *__restrict__ p = c.param[rank] + goff;
     uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
@@ -810,7 +816,8 @@ extern "C" int pr_allreduce(pr_comm *c, int region, uint64_t offset, uint64_t nb
         }
         k = f32 ? (const void *)allreduce_mc_kernel<true> : (const void *)allreduce_mc_kernel<false>;
         // the switch does the summing: a few dozen CTAs keep the links full (4 vectors in flight per thread)
-        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : kMulticastBlocks, k, (nvec + c->world - 1) / c->world / 4 + 1);
+        const int def_blocks = nbytes >= kMulticastLargeBytes ? kMulticastBlocksLarge : kMulticastBlocksSmall;
+        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : def_blocks, k, (nvec + c->world - 1) / c->world / 4 + 1);
         return launch(c, k, grid, stream, d, offset, nvec, scale);
     }
     PR_DISPATCH_W(c->world, k = f32 ? (const void *)allreduce_twoshot_kernel<W_, true>
@@ -861,7 +868,7 @@ extern "C" int pr_allgather_slices(pr_comm *c, int region, uint64_t offset, uint
     const void *k = nullptr;
     if (use_multicast(c)) {
         k = (const void *)allgather_slices_mc_kernel;
-        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : kMulticastBlocks, k, (nvec + c->world - 1) / c->world);
+        int grid = pick_grid(c, max_blocks > 0 ? max_blocks : kMulticastBlocksLarge, k, (nvec + c->world - 1) / c->world);
         return launch(c, k, grid, (cudaStream_t)stream_, d, offset, nvec);
     }
     PR_DISPATCH_W(c->world, k = (const void *)allgather_slices_kernel<W_>);

@@ -174,9 +174,14 @@ class GradSync:
                                "(reference semantics: find_unused_parameters=False)")
         return True
 
-    def reduce_and_step(self, *, lr, beta1, beta2, eps, weight_decay, step, numerics) -> None:
+    def reduce_and_step(self, *, lr, beta1, beta2, eps, weight_decay, step, numerics, max_grad_norm=None,
+                        norm=None) -> None:
         arena = self.arena
         cur = torch.cuda.current_stream()
+        if max_grad_norm and self.world > 1 and self.mode != "replicated":
+            self._reduce_clip_step(lr=lr, beta1=beta1, beta2=beta2, eps=eps, weight_decay=weight_decay, step=step,
+                                   numerics=numerics, max_grad_norm=max_grad_norm, norm=norm)
+            return
         events = getattr(self, "kernel_events", None)          # bench.py: CUDA events around the update kernel
         if events is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -216,12 +221,52 @@ class GradSync:
                                         max_blocks=self.max_blocks, stream=cur)
             if events is not None:
                 e0.record(cur)
+            coef = None
+            if max_grad_norm:
+                # after the exchange every rank holds the same mean gradient, bit for bit: each computes
+                # the same norm from it, deterministically -- no second collective for the scalar
+                norm.compute(arena.g, max_grad_norm)
+                coef = norm.coef
             K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
-                     weight_decay=weight_decay, step=step, numerics=numerics)
+                     weight_decay=weight_decay, step=step, numerics=numerics, grad_scale_dev=coef)
             if events is not None:
                 e1.record(cur)
                 events.append((e0, e1))
         # re-arm for the next backward
+        self._seen = 0
+        self._next_bucket = 0
+        for b in self._buckets:
+            b["pending"] = len(b["members"])
+        if self.comm.timed_out():
+            raise RuntimeError("GradSync: a peer did not reach the gradient exchange (barrier timed out)")
+
+    def _reduce_clip_step(self, *, lr, beta1, beta2, eps, weight_decay, step, numerics, max_grad_norm, norm) -> None:
+        """Clipping with sharded optimizer state ("fused" / "overlap" requested): the global norm is
+        needed before any element is updated, so the single fused launch becomes allreduce (K1) ->
+        norm of the mean gradient (identical on every rank) -> K2 on the rank's own slice with the
+        coefficient read on the device -> all-gather of the updated parameters."""
+        if self.mode == "overlap":
+            raise NotImplementedError("gradient clipping needs every gradient before the first update: "
+                                      "use --grad-sync fused or replicated with --clip-grad-norm")
+        if numerics != 0 or self.arena.dtype != torch.bfloat16:
+            raise RuntimeError("fused GradSync implements bf16 arenas with fp32 op-math (fused=True)")
+        arena = self.arena
+        cur = torch.cuda.current_stream()
+        events = getattr(self, "kernel_events", None)
+        if events is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+        self.comm.allreduce(REGION_G, 0, arena.layout.nbytes, arena.dtype, 1.0 / self.world,
+                            max_blocks=self.max_blocks, stream=cur)
+        norm.compute(arena.g, max_grad_norm)
+        lo, hi = self.slice_range()
+        K.adamw_(arena.p[lo:hi], arena.g[lo:hi], arena.m[lo:hi], arena.v[lo:hi], lr=lr, beta1=beta1, beta2=beta2,
+                 eps=eps, weight_decay=weight_decay, step=step, numerics=0, grad_scale_dev=norm.coef)
+        self.comm.allgather_slices(REGION_P, 0, arena.layout.nbytes, max_blocks=self.max_blocks, stream=cur)
+        if events is not None:
+            e1.record(cur)
+            events.append((e0, e1))
+        self._moments_replicated = False
         self._seen = 0
         self._next_bucket = 0
         for b in self._buckets:
@@ -243,23 +288,52 @@ class GradSync:
                 self.comm.allgather_slices(REGION_V, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
             self._moments_replicated = True
 
+    def _ownership_ranges(self):
+        """Element ranges over which slices are cut: the whole arena ("replicated", "fused") or every
+        bucket ("overlap": one fused launch, hence one set of W slices, per bucket)."""
+        if self.mode == "overlap":
+            return [(b["lo"], b["hi"]) for b in self._buckets]
+        return [(0, self.arena.numel)]
+
+    def owned_ranges(self, rank: Optional[int] = None, world: Optional[int] = None):
+        """Element ranges [lo, hi) of the flat arenas whose optimizer state rank `rank` owns -- its
+        reduce-scatter slices, which are also its checkpoint shard (no re-replication before a
+        sharded save)."""
+        r = self.rank if rank is None else rank
+        w = self.world if world is None else world
+        if w != self.world:          # a layout for another world size: plain arena slices
+            ranges = [(0, self.arena.numel)]
+        else:
+            ranges = self._ownership_ranges()
+        esize = self.arena.layout.esize
+        out = []
+        for lo, hi in ranges:
+            nvec = (hi - lo) * esize // 16
+            per = (nvec + w - 1) // w
+            a = lo + min(per * r, nvec) * 16 // esize
+            b = lo + min(per * (r + 1), nvec) * 16 // esize
+            if b > a:
+                out.append((a, b))
+        return out
+
     def allgather_arena(self, name: str, t: torch.Tensor) -> None:
-        """Every rank holds its `slice_range()` of the flat arena tensor `t` (p, m or v); make every
+        """Every rank holds its `owned_ranges()` of the flat arena tensor `t` (p, m or v); make every
         rank hold all of it.  Symmetric arenas are gathered in place by K1's all-gather kernel;
         a plain tensor (replicated mode keeps p / m / v outside the communicator) bounces through
         the gradient arena, whose contents are dead outside backward."""
         if self.world == 1:
             return
         arena = self.arena
-        nbytes = arena.layout.nbytes
+        esize = arena.layout.esize
         symmetric = name == "g" or self.mode in ("fused", "overlap")
-        if symmetric:
-            self.comm.allgather_slices(_REGION[name], 0, nbytes, max_blocks=self.max_blocks)
-            return
-        lo, hi = self.slice_range()
-        arena.g[lo:hi].copy_(t[lo:hi])
-        self.comm.allgather_slices(REGION_G, 0, nbytes, max_blocks=self.max_blocks)
-        t.copy_(arena.g)
+        region = _REGION[name] if symmetric else REGION_G
+        if not symmetric:
+            for lo, hi in self.owned_ranges():
+                arena.g[lo:hi].copy_(t[lo:hi])
+        for lo, hi in self._ownership_ranges():
+            self.comm.allgather_slices(region, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
+        if not symmetric:
+            t.copy_(arena.g)
 
     def moments_loaded(self) -> None:
         self._moments_replicated = True

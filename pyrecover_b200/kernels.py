@@ -38,14 +38,22 @@ def launch_count() -> int:
 # ------------------------------------------------------------------------- K2 AdamW -----
 
 def adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, numerics=0,
-               grad_dtype=_lib.PR_BF16) -> AdamWArgs:
+               grad_dtype=_lib.PR_BF16, grad_scale_dev: Optional[torch.Tensor] = None) -> AdamWArgs:
+    """grad_scale_dev: a 1-element fp32 CUDA tensor (e.g. GradNorm.coef) multiplied into grad_scale on
+    the device when the kernel starts; the caller keeps it alive until the launch has run."""
+    ptr = None
+    if grad_scale_dev is not None:
+        if not (grad_scale_dev.is_cuda and grad_scale_dev.dtype == torch.float32 and grad_scale_dev.numel() == 1):
+            raise TypeError("grad_scale_dev must be a 1-element fp32 CUDA tensor")
+        ptr = grad_scale_dev.data_ptr()
     return AdamWArgs(float(lr), float(beta1), float(beta2), float(eps), float(weight_decay),
-                     float(grad_scale), int(step), int(numerics), int(grad_dtype))
+                     float(grad_scale), int(step), int(numerics), int(grad_dtype), ptr)
 
 
 def adamw_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, *, lr: float,
            beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8, weight_decay: float = 0.01,
-           step: int = 1, grad_scale: float = 1.0, numerics: int = 0, stream=None) -> None:
+           step: int = 1, grad_scale: float = 1.0, numerics: int = 0, stream=None,
+           grad_scale_dev: Optional[torch.Tensor] = None) -> None:
     """One flat AdamW update, in place on p, m, v (reference train.py:274)."""
     _require_cuda(p, g, m, v)
     n = p.numel()
@@ -53,9 +61,36 @@ def adamw_(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, *
         raise ValueError("p, g, m, v must have the same number of elements")
     if m.dtype != p.dtype or v.dtype != p.dtype:
         raise TypeError("m and v must have the dtype of p")
-    a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, dtype_code(g.dtype))
+    a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, dtype_code(g.dtype), grad_scale_dev)
     check(lib().pr_adamw(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), n, dtype_code(p.dtype),
                          ctypes.byref(a), stream_ptr(stream)), "pr_adamw")
+
+
+class GradNorm:
+    """Device-side result of pr_grad_norm: out = [total norm, clip coefficient, non-finite flag]
+    (fp32) plus the caller-owned scratch the two launches need.  Nothing here synchronises."""
+
+    def __init__(self, device):
+        self.out = torch.zeros(4, dtype=torch.float32, device=device)
+        self.scratch = torch.zeros(_lib.PR_GRAD_NORM_SCRATCH, dtype=torch.float64, device=device)
+
+    @property
+    def norm(self) -> torch.Tensor:
+        return self.out[0:1]
+
+    @property
+    def coef(self) -> torch.Tensor:
+        return self.out[1:2]
+
+    @property
+    def nonfinite(self) -> torch.Tensor:
+        return self.out[2:3]
+
+    def compute(self, g: torch.Tensor, max_norm: float, prescale: float = 1.0, stream=None) -> None:
+        """Flat gradient buffer (pr_grad_norm; reference utils.py:84-89)."""
+        _require_cuda(g)
+        check(lib().pr_grad_norm(g.data_ptr(), g.numel(), dtype_code(g.dtype), float(prescale), float(max_norm),
+                                 self.out.data_ptr(), self.scratch.data_ptr(), stream_ptr(stream)), "pr_grad_norm")
 
 
 class AdamWPlan:
@@ -70,13 +105,22 @@ class AdamWPlan:
         check(lib().pr_adamw_plan_create(offs, lens, n, int(arena_elems), ctypes.byref(self._h)), "pr_adamw_plan_create")
         self._ptrs = (c_void_p * n)()
 
+    def grad_norm(self, grads: Sequence[torch.Tensor], norm: "GradNorm", max_norm: float, prescale: float = 1.0,
+                  stream=None) -> None:
+        """Global L2 norm + clip coefficient of the gradients where autograd left them (pr_grad_norm_scattered)."""
+        for i, g in enumerate(grads):
+            self._ptrs[i] = g.data_ptr()
+        check(lib().pr_grad_norm_scattered(self._h, self._ptrs, float(prescale), float(max_norm), norm.out.data_ptr(),
+                                           norm.scratch.data_ptr(), stream_ptr(stream)), "pr_grad_norm_scattered")
+
     def step(self, p: torch.Tensor, grads: Sequence[torch.Tensor], m: torch.Tensor, v: torch.Tensor, *, lr, beta1=0.9,
-             beta2=0.999, eps=1e-8, weight_decay=0.01, step=1, grad_scale=1.0, numerics=0, stream=None) -> None:
+             beta2=0.999, eps=1e-8, weight_decay=0.01, step=1, grad_scale=1.0, numerics=0, stream=None,
+             grad_scale_dev: Optional[torch.Tensor] = None) -> None:
         """grads[i]: contiguous, 16-B aligned bf16 CUDA tensor holding tensor i's gradient."""
         _require_cuda(p, m, v)
         for i, g in enumerate(grads):
             self._ptrs[i] = g.data_ptr()
-        a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, _lib.PR_BF16)
+        a = adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale, numerics, _lib.PR_BF16, grad_scale_dev)
         check(lib().pr_adamw_scattered(self._h, p.data_ptr(), self._ptrs, m.data_ptr(), v.data_ptr(), ctypes.byref(a),
                                        stream_ptr(stream)), "pr_adamw_scattered")
 

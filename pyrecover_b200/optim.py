@@ -31,7 +31,8 @@ class B200AdamW(torch.optim.Optimizer):
     def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-2, amsgrad: bool = False, *, maximize: bool = False,
                  foreach: Optional[bool] = None, capturable: bool = False, differentiable: bool = False,
-                 fused: Optional[bool] = None, numerics: Optional[int] = None, grad_sync=None):
+                 fused: Optional[bool] = None, numerics: Optional[int] = None, grad_sync=None,
+                 max_grad_norm: Optional[float] = None):
         if amsgrad or maximize or capturable or differentiable:
             raise NotImplementedError("B200AdamW implements the reference configuration only "
                                       "(amsgrad/maximize/capturable/differentiable = False)")
@@ -41,6 +42,13 @@ class B200AdamW(torch.optim.Optimizer):
             raise ValueError("invalid AdamW hyper-parameter")
         self._numerics_override = numerics
         self._grad_sync = grad_sync
+        # global-norm clipping folded into the update (reference utils.py:84-89, call commented out at
+        # train.py:271-272): the norm is two small launches over the gradients, the coefficient stays
+        # on the device and K2 multiplies it in -- no host sync, no extra pass, no re-rounded gradients
+        if max_grad_norm is not None and not max_grad_norm > 0:
+            raise ValueError("max_grad_norm must be positive (None disables clipping)")
+        self.max_grad_norm = max_grad_norm
+        self._grad_norm: Optional[K.GradNorm] = None
         self._arenas: List[FlatArena] = []
         self._steps: List[int] = []
         self._step_tensors: List[torch.Tensor] = []
@@ -84,6 +92,16 @@ class B200AdamW(torch.optim.Optimizer):
     def arenas(self) -> List[FlatArena]:
         return self._arenas
 
+    def grad_norm_state(self) -> Optional[K.GradNorm]:
+        """Device-side [norm, coefficient, non-finite flag] of the last clipped step (None when
+        clipping is off).  Reading it synchronises; do it at logging frequency."""
+        return self._grad_norm
+
+    def _norm_buffers(self) -> K.GradNorm:
+        if self._grad_norm is None:
+            self._grad_norm = K.GradNorm(self._arenas[0].device)
+        return self._grad_norm
+
     def _numerics(self, group) -> int:
         if self._numerics_override is not None:
             return int(self._numerics_override)
@@ -113,7 +131,8 @@ class B200AdamW(torch.optim.Optimizer):
                 self._step_tensors[gi].fill_(self._steps[gi])
                 self._grad_sync.reduce_and_step(
                     lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"], weight_decay=group["weight_decay"],
-                    step=self._steps[gi], numerics=self._numerics(group))
+                    step=self._steps[gi], numerics=self._numerics(group),
+                    max_grad_norm=self.max_grad_norm, norm=self._norm_buffers() if self.max_grad_norm else None)
                 continue
             have = [q.grad is not None for q in arena.params]
             if not any(have):
@@ -131,17 +150,27 @@ class B200AdamW(torch.optim.Optimizer):
             if events is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
+            coef = None
+            if self.max_grad_norm:
+                if len(self._arenas) != 1:
+                    raise NotImplementedError("gradient clipping supports a single param group (as the reference uses)")
+                coef = self._norm_buffers().coef
             if scattered:
                 # world size 1: read every gradient where autograd left it -- no copy into the g arena
                 if self._plans[gi] is None:
                     self._plans[gi] = K.AdamWPlan([s.offset for s in arena.layout.slots],
                                                   [s.numel for s in arena.layout.slots], arena.numel)
+                if coef is not None:
+                    self._plans[gi].grad_norm(grads, self._grad_norm, self.max_grad_norm)
                 self._plans[gi].step(arena.p, grads, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2,
                                      eps=group["eps"], weight_decay=group["weight_decay"], step=self._steps[gi],
-                                     numerics=self._numerics(group))
+                                     numerics=self._numerics(group), grad_scale_dev=coef)
             else:
+                if coef is not None:
+                    self._grad_norm.compute(arena.g, self.max_grad_norm)
                 K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
-                         weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group))
+                         weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group),
+                         grad_scale_dev=coef)
             if events is not None:
                 e1.record()
                 events.append((e0, e1))

@@ -209,18 +209,24 @@ class Snapshotter:
         return self._full
 
     def shard_pieces(self, rank: int, world: int) -> List[Tuple[int, int]]:
-        """(global image offset, nbytes) runs that rank `rank` of `world` owns: its element slice
-        of every arena tensor (16-byte granular, the reduce-scatter slice of K1); rank 0 also owns
-        the stray tensors."""
+        """(global image offset, nbytes) runs that rank `rank` of `world` owns: its element ranges
+        of every arena tensor -- the reduce-scatter slices of K1 (GradSync.owned_ranges: one slice of
+        the arena, or one per bucket in "overlap" mode), 16-byte granular -- so a sharded save writes
+        the optimizer state where it already lives; rank 0 also owns the stray tensors."""
+        gs = getattr(self.optimizer, "_grad_sync", None)
         runs = []
         for p in self.full_pieces:
             if self._in_arena(p.tensor):
-                nvec = (p.nbytes + 15) // 16
-                per = (nvec + world - 1) // world
-                lo, hi = min(per * rank, nvec) * 16, min(per * (rank + 1), nvec) * 16
-                hi = min(hi, p.nbytes)
-                if hi > lo:
-                    runs.append((p.global_off + lo, hi - lo))
+                esize = p.tensor.element_size()
+                if gs is not None and gs.world == world and gs.arena is not None and p.nbytes == gs.arena.layout.nbytes:
+                    ranges = [(lo * esize, hi * esize) for lo, hi in gs.owned_ranges(rank, world)]
+                else:
+                    nvec = (p.nbytes + 15) // 16
+                    per = (nvec + world - 1) // world
+                    ranges = [(min(per * rank, nvec) * 16, min(min(per * (rank + 1), nvec) * 16, p.nbytes))]
+                for lo, hi in ranges:
+                    if hi > lo:
+                        runs.append((p.global_off + lo, hi - lo))
             elif rank == 0 and p.nbytes:
                 runs.append((p.global_off, p.nbytes))
         return runs
@@ -230,9 +236,10 @@ class Snapshotter:
             if self._shard is not None:
                 self._shard.close()
             pieces, off = [], 0
+            runs = self.shard_pieces(rank, world)
             for p in self.full_pieces:
                 flat = p.tensor.reshape(-1).view(torch.uint8)
-                for goff, n in self.shard_pieces(rank, world):
+                for goff, n in runs:
                     if p.global_off <= goff < p.global_off + max(p.nbytes, 1):
                         lo = goff - p.global_off
                         pieces.append(Piece(flat[lo:lo + n], off, global_off=goff))

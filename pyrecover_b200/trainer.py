@@ -44,7 +44,7 @@ def model_args_from_cli(args, vocab_size: int):
 class Trainer:
     def __init__(self, model: torch.nn.Module, device: torch.device, *, lr: float, fused: bool,
                  warmup_steps: int, world_size: int = 1, local_rank: int = 0,
-                 grad_sync_mode: str = "replicated", process_group=None):
+                 grad_sync_mode: str = "replicated", process_group=None, max_grad_norm: Optional[float] = None):
         from utils import build_lr_scheduler
         self.device, self.world_size = device, world_size
         self.grad_sync = None
@@ -54,13 +54,15 @@ class Trainer:
                 from .gradsync import GradSync
                 self.grad_sync = GradSync(process_group, mode=grad_sync_mode)
             self.model = model
-            self.optimizer = B200AdamW(model.parameters(), lr=lr, fused=fused, grad_sync=self.grad_sync)
+            self.optimizer = B200AdamW(model.parameters(), lr=lr, fused=fused, grad_sync=self.grad_sync,
+                                       max_grad_norm=max_grad_norm)
         else:
             if world_size > 1:
                 from torch.nn.parallel import DistributedDataParallel as DDP
                 model = DDP(model, find_unused_parameters=False)      # reference train.py:107-115
             self.model = model
             self.optimizer = torch.optim.AdamW(model.parameters(), lr=lr, fused=fused)   # train.py:120-122
+        self.max_grad_norm = max_grad_norm
         self.model.train()
         self.lr_scheduler = build_lr_scheduler(self.optimizer, warmup_steps)
 
@@ -73,6 +75,9 @@ class Trainer:
         loss = loss / num_items
         del logits
         loss.backward()
+        if self.max_grad_norm and self.device.type != "cuda":
+            from utils import clip_grad_norm_             # the reference's own call, train.py:271-272
+            clip_grad_norm_(self.model.parameters(), self.max_grad_norm)
         self.optimizer.step()
         self.lr_scheduler.step()
         return loss

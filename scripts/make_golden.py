@@ -15,6 +15,9 @@ these are outputs of the reference's call sites run here):
                                    (reference train.py:110-115): the averaged bf16 gradient.
   ref_vanilla.pt(+.md5)            a checkpoint written by the reference's own
                                    save_ckpt_vanilla (pyrecover/checkpoint.py:25-105).
+  clip_grad_norm.npz               the reference's clip_grad_norm_ (utils.py:84-89, imported from
+                                   /root/reference/utils.py) on fp32 and bf16 gradient lists:
+                                   total norm and the clipped gradients.
   checksum_kat.npz                 PR-SUM64 known answers from an independent pure-python
                                    big-int evaluation of the definition.
 """
@@ -154,8 +157,33 @@ def gen_checksum_kat():
     print("wrote checksum_kat")
 
 
+def gen_clip():
+    """Reference clip_grad_norm_ on seeded gradient lists, fp32 and bf16, above and below the threshold."""
+    sys.path.insert(0, str(REF))
+    ref_utils = sys.modules.get("ref_utils") or _load(REF / "utils.py", "ref_utils")
+    out = {}
+    shapes = [(64, 48), (48,), (300, 17), (5,), (4096,)]
+    cases = [("big", 0.3, 1.0), ("small", 1e-4, 1.0), ("tight", 0.3, 1e-2)]
+    for tag, scale, max_norm in cases:
+        for dtype, dname in ((torch.float32, "f32"), (torch.bfloat16, "bf16")):
+            gen = torch.Generator().manual_seed(hash(tag) % 1000 if False else len(tag) * 17)
+            params = [torch.nn.Parameter(torch.zeros(s, dtype=dtype)) for s in shapes]
+            grads = [(torch.randn(s, generator=gen) * scale).to(dtype) for s in shapes]
+            for q, g in zip(params, grads):
+                q.grad = g.clone()
+            total = ref_utils.clip_grad_norm_(params, max_norm)
+            key = f"{tag}_{dname}"
+            out[key + "_grads"] = np.concatenate([bits(g).reshape(-1) for g in grads])
+            out[key + "_clipped"] = np.concatenate([bits(q.grad).reshape(-1) for q in params])
+            out[key + "_total"] = np.array([float(total)], dtype=np.float64)
+            out[key + "_max_norm"] = np.array([max_norm], dtype=np.float64)
+    np.savez_compressed(OUT / "clip_grad_norm.npz", **out)
+    print("wrote clip_grad_norm.npz")
+
+
 def main():
     OUT.mkdir(parents=True, exist_ok=True)
+    gen_clip()
     gen_adamw(torch.bfloat16, "adamw_bf16.npz")
     gen_adamw(torch.float32, "adamw_f32.npz")
     gen_ddp(2)
@@ -191,5 +219,7 @@ def gen_boundary():
 if __name__ == "__main__":
     if "--boundary-only" in sys.argv:
         gen_boundary()
+    elif "--clip-only" in sys.argv:
+        gen_clip()
     else:
         main()

@@ -82,6 +82,29 @@ def test_two_gpu_multicast_train_resume_weight_equality(tmp_path, mode):
         assert torch.equal(A["optimizer"]["state"][i]["exp_avg_sq"], B["optimizer"]["state"][i]["exp_avg_sq"])
 
 
+def test_two_gpu_gradient_clipping_modes_agree(tmp_path):
+    """--clip-grad-norm at W = 2: the global norm is taken from the exchanged mean gradient, which
+    is bit-identical on both ranks, so "replicated" (allreduce -> norm -> K2 everywhere) and
+    "fused" (allreduce -> norm -> K2 on the own slice -> parameter all-gather) end with the same
+    weights bit for bit; and a tight threshold changes the result (the coefficient is applied)."""
+    _need(2)
+    clip = ("--clip-grad-norm", "--grad-max-norm", "0.05")
+    p2p = {"PR_COMM_MULTICAST": "0"}
+    _launch(tmp_path, "rep", 10, 2, ("--grad-sync", "replicated") + clip, p2p)
+    _launch(tmp_path, "fus", 10, 2, ("--grad-sync", "fused") + clip, p2p)
+    _launch(tmp_path, "noclip", 10, 2, ("--grad-sync", "replicated"), p2p)
+    A = torch.load(tmp_path / "rep" / "ckpt_10.pt", map_location="cpu")
+    B = torch.load(tmp_path / "fus" / "ckpt_10.pt", map_location="cpu")
+    C = torch.load(tmp_path / "noclip" / "ckpt_10.pt", map_location="cpu")
+    differs = False
+    for k in A["model"]:
+        assert torch.equal(A["model"][k], B["model"][k]), k
+        differs = differs or not torch.equal(A["model"][k], C["model"][k])
+    assert differs, "clipping at 0.05 left the weights unchanged"
+    for i in A["optimizer"]["state"]:
+        assert torch.equal(A["optimizer"]["state"][i]["exp_avg"], B["optimizer"]["state"][i]["exp_avg"])
+
+
 def test_two_gpu_matches_vanilla_and_sharded(tmp_path):
     """The same W = 2 run checkpointed in both formats holds the same bytes: the sharded
     directory, loaded on ONE GPU (different world size), equals the vanilla file."""

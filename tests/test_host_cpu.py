@@ -34,7 +34,7 @@ def test_library_builds_loads_and_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(L, name), f"{name} declared in include/pyrecover_b200.h but not exported"
     assert sorted(_lib.EXPORTED_SYMBOLS) == declared, "ctypes table and header disagree"
-    assert L.pr_abi_version() == 1
+    assert L.pr_abi_version() == _lib.PR_ABI_VERSION
     assert L.pr_last_error() is not None
 
 

@@ -127,3 +127,31 @@ def test_reference_written_checkpoint_fixture(golden_dir):
     assert set(ck) == {"epoch", "step", "model", "optimizer", "lr_scheduler"}
     assert ck["step"] == 3 and ck["epoch"] == 1
     assert set(ck["optimizer"]["state"][0]) == {"step", "exp_avg", "exp_avg_sq"}
+
+
+@pytest.mark.parametrize("tag", ["big", "small", "tight"])
+def test_grad_norm_and_clip_vs_reference_clip_grad_norm(oracle, golden_dir, tag):
+    """oracle.grad_norm == the reference's clip_grad_norm_ (utils.py:84-89; vectors made by
+    scripts/make_golden.py --clip-only from /root/reference/utils.py).
+    fp32 gradients: norm within 1e-6 (torch reduces in fp32, the oracle in double) and the clipped
+    gradients g * coef equal to torch's within 1 fp32 ulp.  bf16 gradients: torch rounds every
+    per-tensor norm and the total to bf16 (2^-8 each), which the oracle does not -- 2^-7 stated."""
+    G = _load(golden_dir, "clip_grad_norm.npz")
+    max_norm = float(G[f"{tag}_f32_max_norm"][0])
+    g = G[f"{tag}_f32_grads"]
+    norm, coef, bad = oracle.grad_norm(g, max_norm)
+    total = float(G[f"{tag}_f32_total"][0])
+    assert not bad and abs(norm - total) <= 1e-6 * total
+    assert coef == (1.0 if total + 1e-6 <= max_norm else coef) and 0.0 < coef <= 1.0
+    mine = g * np.float32(coef)
+    assert np.allclose(mine, G[f"{tag}_f32_clipped"], rtol=3e-7, atol=0)
+    if tag == "small":
+        assert coef == 1.0 and np.array_equal(G[f"{tag}_f32_clipped"], g)      # below the threshold: untouched
+    else:
+        assert coef < 1.0
+    gb = G[f"{tag}_bf16_grads"]
+    nb, cb, _ = oracle.grad_norm(gb, max_norm)
+    tb = float(G[f"{tag}_bf16_total"][0])
+    assert abs(nb - tb) <= 2.0 ** -7 * tb
+    # prescale multiplies the norm
+    assert abs(oracle.grad_norm(g, max_norm, prescale=0.25)[0] - 0.25 * norm) <= 1e-6 * norm

@@ -95,7 +95,8 @@ def train(args):
         model = torch.compile(model, fullgraph=True)
     trainer = Trainer(model, device, lr=args.learning_rate, fused=args.fused_optimizer,
                       warmup_steps=args.lr_warmup_steps, world_size=world_size, local_rank=local_rank,
-                      grad_sync_mode=args.grad_sync)
+                      grad_sync_mode=args.grad_sync,
+                      max_grad_norm=args.grad_max_norm if args.clip_grad_norm else None)
     model, optimizer, lr_scheduler = trainer.model, trainer.optimizer, trainer.lr_scheduler
     num_flop_per_token = get_num_flop_per_token(get_num_params(model, exclude_embedding=True), model_config)
 

@@ -69,6 +69,9 @@ _ADDITIVE_FLAGS = [
                          help="replicated: P2P allreduce + AdamW on every rank; fused: one reduce-scatter+AdamW+all-gather "
                               "kernel after backward; overlap: the fused kernel per bucket, under backward")),
     ("--snapshot-mode", dict(type=str, default=None, choices=[None, "staged", "direct"])),
+    ("--clip-grad-norm", dict(action="store_true",
+                              help="clip the global gradient norm to --grad-max-norm (the call the reference left "
+                                   "commented out at train.py:271-272), folded into the optimizer kernel")),
     ("--sync-checkpoints", dict(action="store_true", help="wait for each checkpoint to be durable before continuing")),
 ]
 
