@@ -173,6 +173,7 @@ class Snapshotter:
         self._writer: Optional[threading.Thread] = None
         self._writer_error: Optional[BaseException] = None
         self._stub_cache: Dict[Any, PT.TensorStub] = {}
+        self._layout: Optional[Dict[str, Any]] = None
         self.last_stats: Dict[str, Any] = {}
         # ---- full image layout: one record per dtype; arenas first (p | m | v), extras after ----
         by_dtype: "OrderedDict[torch.dtype, List[torch.Tensor]]" = OrderedDict()
@@ -296,6 +297,29 @@ class Snapshotter:
             return tuple(self.stubify(v, small) for v in obj)
         return copy.deepcopy(obj)
 
+    def tensor_layout(self) -> Dict[str, Any]:
+        """Where every tensor of model.state_dict() and of the optimizer state sits in the full image:
+        {"model": {name: [dtype, byte offset, shape]}, "optimizer": {index: {"exp_avg": [...],
+        "exp_avg_sq": [...]}}}.  Static for the job; stored in a sharded directory's meta.pt so that
+        the directory can be read back WITHOUT this library or a GPU (pyrecover/convert.py)."""
+        if self._layout is None:
+            def where(t: torch.Tensor):
+                loc = self._locate(t) if t.is_cuda and t.is_contiguous() else None
+                if loc is None:
+                    return None
+                rec = self.records[loc[0]]
+                return [str(t.dtype).replace("torch.", ""), rec["off"] + loc[1] * t.element_size(), list(t.shape)]
+            model = {k: where(t) for k, t in self.module.state_dict().items()}
+            opt: Dict[int, Any] = {}
+            idx = 0
+            for group in self.optimizer.param_groups:
+                for q in group["params"]:
+                    st = self.optimizer.state.get(q, {})
+                    opt[idx] = {k: where(st[k]) for k in ("exp_avg", "exp_avg_sq") if k in st}
+                    idx += 1
+            self._layout = {"model": model, "optimizer": opt, "image_bytes": self.full_bytes}
+        return self._layout
+
     # ------------------------------------------------------------------ writer plumbing ---
     def wait(self) -> None:
         """Join the writer of the previous save (durability point); re-raise its failure."""
@@ -398,6 +422,8 @@ class Snapshotter:
         e_read, e_copied = img.stage(self.side)
         self._fence_optimizer(e_read)
         small_state = _to_cpu(small_state)
+        if rank == 0:
+            small_state["layout"] = self.tensor_layout()
         d = Path(dirpath)
         self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
 

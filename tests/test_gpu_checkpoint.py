@@ -214,6 +214,42 @@ def test_sharded_save_load_roundtrip(cuda_lib, tmp_path, world):
     ck.release_checkpoint_engines()
 
 
+def test_sharded_directory_converts_offline_to_vanilla_and_dcp(cuda_lib, tmp_path):
+    """pyrecover.convert reads a sharded directory with nothing but torch on the CPU (the layout table
+    travels in meta.pt): the vanilla file it writes equals save_ckpt_vanilla's tensors, loads back
+    through load_ckpt_vanilla, and the DCP directory it writes loads with torch.distributed.checkpoint."""
+    import pyrecover
+    from pyrecover import checkpoint as ck
+    from pyrecover import convert
+    model, opt, sched = _build()
+    _run_steps(model, opt, sched, 3)
+    d = tmp_path / "exp" / "ckpt_3"
+    pyrecover.save_ckpt_distributed(model, opt, sched, None, 3, 1, d, max_keep=3, verify=True)
+    pyrecover.save_ckpt_vanilla(model, opt, sched, None, 3, 1, tmp_path / "direct.pt", max_keep=0, verify=False)
+    ck.wait_for_checkpoints()
+    state = convert.load_state_cpu(str(d))
+    direct = torch.load(tmp_path / "direct.pt", map_location="cpu")
+    assert list(state["model"]) == list(direct["model"]) and state["step"] == 3 and state["epoch"] == 1
+    for k in direct["model"]:
+        assert torch.equal(state["model"][k], direct["model"][k]), k
+    for i, st in direct["optimizer"]["state"].items():
+        for key in ("exp_avg", "exp_avg_sq"):
+            assert torch.equal(state["optimizer"]["state"][i][key], st[key]), (i, key)
+        assert float(state["optimizer"]["state"][i]["step"]) == float(st["step"])
+    assert state["optimizer"]["param_groups"][0]["params"] == direct["optimizer"]["param_groups"][0]["params"]
+    assert convert.main([str(d), str(tmp_path / "conv.pt"), "--to", "vanilla"]) == 0
+    m2, o2, s2 = _build(seed=9)
+    assert pyrecover.load_ckpt_vanilla(m2, o2, s2, None, str(tmp_path / "conv.pt"), verify=False) == (1, 3)
+    assert _equal_models(m2, model) and torch.equal(o2.arenas[0].m, opt.arenas[0].m) and o2._steps[0] == 3
+    assert convert.main([str(d), str(tmp_path / "dcp" / "ckpt_3"), "--to", "dcp"]) == 0
+    import torch.distributed.checkpoint as dcp
+    tmpl = {"model": {k: torch.zeros_like(v) for k, v in direct["model"].items()}}
+    dcp.load(state_dict=tmpl, checkpoint_id=str(tmp_path / "dcp" / "ckpt_3"), no_dist=True)
+    for k in direct["model"]:
+        assert torch.equal(tmpl["model"][k], direct["model"][k]), k
+    ck.release_checkpoint_engines()
+
+
 def _train(tmp, name, extra, steps):
     cmd = [sys.executable, str(ROOT / "train.py"), "--synthetic-data", "--model-preset", "tiny", "--sequence-length", "256",
            "--training-steps", str(steps), "--checkpoint-frequency", "10", "--checkpoint-dir", str(tmp), "--experiment_name", name,
