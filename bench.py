@@ -339,7 +339,7 @@ def run_b200(a):
                       "frac_of_measured": bus / 770.0, "frac_of_nominal": bus / 900.0}
         traffic = None
         tf = ROOT / "profiles" / "k2_traffic.json"
-        if tf.exists():
+        if tf.exists() and world == 1:            # the ncu capture is of the single-GPU K2
             traffic = json.loads(tf.read_text()).get("dram_bytes_per_launch")
         line = {
             "metric": METRIC, "value": tokens_per_step * a.steps / (ms * 1e-3), "unit": "tokens/s", "n_gpus": world,
