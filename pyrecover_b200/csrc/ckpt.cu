@@ -189,13 +189,18 @@ pack_kernel(PlanDev pd, uint8_t *image, uint64_t *sum) {
     if (WITH_SUM) block_sum_commit(A, B, sum);
 }
 
-int ckpt_blocks_per_sm() {
-    static int v = [] {
+// Resident CTAs per SM, measured on B200 over 2 GiB tensors (round 1): the copy-shaped pack / unpack
+// kernels peak with FEW concurrent streams (3 CTAs/SM: 6300 GB/s = 0.98 of the measured copy peak;
+// 8: 0.93), the read-only checksum with many (12: 6855 GB/s; 3: 5401).  PR_CKPT_BLOCKS_PER_SM
+// overrides both.
+int ckpt_blocks_per_sm(bool copy_shaped) {
+    static int env = [] {
         const char *e = getenv("PR_CKPT_BLOCKS_PER_SM");
-        int b = e ? atoi(e) : 8;
-        return b > 0 ? b : 8;
+        int b = e ? atoi(e) : 0;
+        return b > 0 ? b : 0;
     }();
-    return v;
+    if (env) return env;
+    return copy_shaped ? 3 : 12;
 }
 
 }  // namespace
@@ -217,7 +222,7 @@ extern "C" int pr_checksum(const void *data, uint64_t nbytes, uint64_t word_base
     cudaStream_t stream = (cudaStream_t)stream_;
     uint64_t nvec = (nbytes + 15) / 16;
     uint64_t need = (nvec + (uint64_t)kThreads * kUnroll - 1) / ((uint64_t)kThreads * kUnroll);
-    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm();
+    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm(false);
     int grid = (int)(need < cap ? need : cap);
     if (pr_aligned16(data))
         checksum_kernel<<<grid, kThreads, 0, stream>>>((const uint8_t *)data, nbytes, word_base, sum);
@@ -320,7 +325,7 @@ static int launch_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, voi
     PR_REQUIRE(image != nullptr && pr_aligned16(image), "pr_ckpt_%s: image must be non-NULL and 16-B aligned",
                UNPACK ? "unpack" : "pack");
     cudaStream_t stream = (cudaStream_t)stream_;
-    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm();
+    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm(true);
     int grid = (int)(plan->dev.ntiles < cap ? plan->dev.ntiles : cap);
     if (sum)
         pack_kernel<UNPACK, true><<<grid, kThreads, 0, stream>>>(plan->dev, (uint8_t *)image, sum);
@@ -531,7 +536,7 @@ extern "C" int pr_ckpt_pack_noalloc(const void *const *tensor, const uint64_t *n
     pd.tile_first = reinterpret_cast<const uint64_t *>(base + 3 * kNoAllocSegBytes);
     pd.tile_seg = reinterpret_cast<const uint32_t *>(base + 4 * kNoAllocSegBytes);
     pd.ntiles = ntiles;
-    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm();
+    uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm(true);
     int grid = (int)(ntiles < cap ? ntiles : cap);
     if (sum)
         pack_kernel<false, true><<<grid, kThreads, 0, stream>>>(pd, (uint8_t *)image, sum);
