@@ -41,6 +41,16 @@ REGION_G, REGION_P, REGION_M, REGION_V = 0, 1, 2, 3
 _REGION = {"g": REGION_G, "p": REGION_P, "m": REGION_M, "v": REGION_V}
 
 
+def slice_of(lo: int, hi: int, esize: int, rank: int, world: int):
+    """Rank `rank`'s slice [a, b) of the element range [lo, hi) cut into `world` runs of whole 16-byte
+    vectors -- the partition K1's kernels use (csrc/allreduce.cu slice_bounds: per = ceil(nvec / W))."""
+    nvec = (hi - lo) * esize // 16
+    per = (nvec + world - 1) // world
+    a = lo + min(per * rank, nvec) * 16 // esize
+    b = lo + min(per * (rank + 1), nvec) * 16 // esize
+    return a, b
+
+
 class GradSync:
     def __init__(self, process_group=None, mode: str = "replicated", bucket_bytes: int = 256 << 20,
                  overlap: bool = True, max_blocks: int = 0, overlap_blocks: int = 32,
@@ -308,10 +318,7 @@ class GradSync:
         esize = self.arena.layout.esize
         out = []
         for lo, hi in ranges:
-            nvec = (hi - lo) * esize // 16
-            per = (nvec + w - 1) // w
-            a = lo + min(per * r, nvec) * 16 // esize
-            b = lo + min(per * (r + 1), nvec) * 16 // esize
+            a, b = slice_of(lo, hi, esize, r, w)
             if b > a:
                 out.append((a, b))
         return out
@@ -341,11 +348,7 @@ class GradSync:
     def slice_range(self, rank: Optional[int] = None):
         """Element range [lo, hi) of the arena a rank owns (reduce-scatter slice; checkpoint shard)."""
         r = self.rank if rank is None else rank
-        nvec = self.arena.numel * self.arena.layout.esize // 16
-        per = (nvec + self.world - 1) // self.world
-        per_el = per * 16 // self.arena.layout.esize
-        lo = min(per_el * r, self.arena.numel)
-        return lo, min(lo + per_el, self.arena.numel)
+        return slice_of(0, self.arena.numel, self.arena.layout.esize, r, self.world)
 
     def close(self) -> None:
         for h in self._hooks:

@@ -371,6 +371,40 @@ def test_config1_gloo_world2_resume_weight_equality(tmp_path, sharded):
         assert float((A[k].float() - B[k].float()).abs().max()) == 0.0, k
 
 
+def test_slice_partition_covers_every_range_once():
+    """The reduce-scatter / shard partition (gradsync.slice_of == csrc/allreduce.cu slice_bounds): for
+    every world size the W slices tile the range exactly, on 16-byte boundaries."""
+    from pyrecover_b200.gradsync import slice_of
+    for esize in (2, 4):
+        for lo, hi in ((0, 1024 * 8), (4096, 4096 + 8 * 1000), (0, 8 * 7), (128, 128)):
+            for world in range(1, 9):
+                cur = lo
+                for r in range(world):
+                    a, b = slice_of(lo, hi, esize, r, world)
+                    assert a == cur and b >= a and (a - lo) * esize % 16 == 0
+                    cur = b
+                assert cur == lo + (hi - lo) * esize // 16 * 16 // esize
+
+
+def test_clip_grad_norm_flag_on_the_host_path(tmp_path):
+    """--clip-grad-norm on a CPU model runs the reference's own clip_grad_norm_ (utils.py:84-89) at the
+    call site the reference left commented out (train.py:271-272); a tight threshold changes the run."""
+    def run(name, extra):
+        cmd = [sys.executable, str(ROOT / "train.py"), "--device", "cpu", "--synthetic-data", "--model-preset", "tiny",
+               "--sequence-length", "32", "--batch-size", "1", "--training-steps", "4", "--checkpoint-frequency", "4",
+               "--checkpoint-dir", str(tmp_path), "--experiment_name", name, "--logging-frequency", "2",
+               "--learning-rate", "1e-3", *extra]
+        r = subprocess.run(cmd, cwd=str(ROOT), env=dict(os.environ, OMP_NUM_THREADS="2"), capture_output=True, text=True,
+                           timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+        return torch.load(tmp_path / name / "ckpt_4.pt", map_location="cpu")["model"]
+    A = run("plain", ())
+    B = run("clip", ("--clip-grad-norm", "--grad-max-norm", "0.01"))
+    C = run("loose", ("--clip-grad-norm", "--grad-max-norm", "1e6"))
+    assert any(not torch.equal(A[k], B[k]) for k in A)
+    assert all(torch.equal(A[k], C[k]) for k in A)          # coefficient clamps to 1: nothing changes
+
+
 # ------------------------------------------------------------------------- converter ------
 def test_convert_reference_vanilla_to_dcp_and_back(tmp_path, golden_dir):
     """pyrecover.convert on the CPU: a checkpoint written by the REFERENCE's save_ckpt_vanilla becomes a
