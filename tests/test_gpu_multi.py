@@ -82,6 +82,32 @@ def test_two_gpu_multicast_train_resume_weight_equality(tmp_path, mode):
         assert torch.equal(A["optimizer"]["state"][i]["exp_avg_sq"], B["optimizer"]["state"][i]["exp_avg_sq"])
 
 
+@pytest.mark.parametrize("multicast", ["0", "1"])
+def test_two_gpu_allreduce_kernels_parity(tmp_path, multicast):
+    """K1 over real NVLink at W = 2 (scripts/allreduce_bench.py, small sizes): P2P two-shot / one-shot
+    bit-exact against the fp32 rank-order sum on every rank, the fused kernel bit-equal to
+    allreduce -> K2; with the NVSwitch multicast kernels forced on: within 1 bf16 ulp + the
+    summation-order term, identical across ranks and from run to run, fp32 payload within its bound,
+    fused multicast bit-equal to multicast allreduce -> K2."""
+    _need(2)
+    import json
+    out = tmp_path / "ar.json"
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", PR_COMM_TIMEOUT_S="30", PR_COMM_MULTICAST=multicast)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(29900 + (os.getpid() % 90)), str(ROOT / "scripts" / "allreduce_bench.py"),
+           "--min-log2", "21", "--max-log2", "23", "--mc-blocks", "16", "--json", str(out)]
+    r = subprocess.run(cmd, cwd=str(ROOT), env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-5000:]
+    res = json.loads(out.read_text())
+    assert res["parity_two_shot"] and res["parity_one_shot"] and res["parity_fused"]
+    if multicast == "1" and res["multicast_available"]:
+        assert res["parity_multimem_within_bound"] and res["multimem_identical_across_ranks"]
+        assert res["multimem_deterministic"] and res["parity_multimem_f32"] and res["parity_fused_multimem"]
+        assert max(abs(int(k)) for k, v in res["multimem_ulp_diff_hist"].items() if v) <= 1
+    if multicast == "0":
+        assert not res["multicast_available"]
+
+
 def test_two_gpu_gradient_clipping_modes_agree(tmp_path):
     """--clip-grad-norm at W = 2: the global norm is taken from the exchanged mean gradient, which
     is bit-identical on both ranks, so "replicated" (allreduce -> norm -> K2 everywhere) and
