@@ -650,6 +650,7 @@ static int import_vmm(pr_comm *c, const Blob *blobs) {
     int nreg = 0, reg_ids[PR_MAX_REGIONS];
     for (int k = 0; k < PR_MAX_REGIONS; ++k)
         if (c->region_bytes[k]) reg_ids[nreg++] = k;
+    if (nreg == 0) return PR_OK;                 // nothing to share (every rank sees the same region set)
     bool mc = true;
     for (int r = 0; r < c->world; ++r) mc = mc && blobs[r].want_mc;
     int fds[2 * PR_MAX_REGIONS], nfds = 0;
