@@ -17,11 +17,15 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kUnroll = 2;
-constexpr int kMinBlocks = 4;    // <= 64 registers per thread: 32 resident warps per SM
+constexpr int kMinBlocks = 3;    // <= 85 registers per thread, 24 resident warps per SM (the grid is sized for 3 CTAs/SM anyway)
 // CTAs per SM the grid is sized for.  Measured on B200, 128 MiB - 8 GiB arenas (round 1): 3 CTAs/SM give
 // 0.95 - 0.98 of the measured HBM copy peak (6310 GB/s at 2 GiB), 4 give 0.87 - 0.92, 5 give 0.78: with four
 // streams per thread fewer concurrent CTAs keep more DRAM pages open.  PR_ADAMW_BLOCKS_PER_SM overrides.
 constexpr int kDefaultBlocksPerSM = 3;
+#ifndef PR_STEPWISE_FAST
+#define PR_STEPWISE_FAST 1
+#endif
+constexpr bool kStepwiseFast = PR_STEPWISE_FAST != 0;   // numerics 1 through the branch-free sequences (0: IEEE intrinsics)
 
 template <bool GRAD_F32>
 __device__ __forceinline__ void load_grad8(const void *g_, uint64_t j, float (&g)[8]) {
@@ -41,6 +45,7 @@ template <int NUMERICS>
 __device__ __forceinline__ void update_vec8(uint4 &P, const float (&g)[8], uint4 &M, uint4 &V,
                                             const AdamWConsts &c, const AdamWFast &f) {
     if (NUMERICS == 0) adamw_vec8_fast(P, g, M, V, f);
+    else if (kStepwiseFast) adamw_vec8_stepwise_fast(P, g, M, V, f);
     else adamw_vec8<NUMERICS>(P, g, M, V, c);
 }
 
