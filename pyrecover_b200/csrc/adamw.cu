@@ -148,8 +148,10 @@ struct AdamWPlanDev {
     const uint32_t *tile_seg;     // tile -> tensor
 };
 
+// numerics 0 fits 64 registers without spilling and measured 1 % faster that way inside the training step
+// (2.38 vs 2.41 ms); the stepwise numerics needs the 85 that 3 CTAs/SM allow
 template <int NUMERICS>
-__global__ void __launch_bounds__(kThreads, kMinBlocks)
+__global__ void __launch_bounds__(kThreads, NUMERICS == 0 ? 4 : kMinBlocks)
 adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, uint16_t *__restrict__ v,
                             AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
                             const __grid_constant__ GradPtrs gp, AdamWConsts c_) {
