@@ -7,9 +7,10 @@ allreduce its Reducer fires inside `loss.backward()` (train.py:269):
   * construction broadcasts rank 0's parameters to every rank (DDP's _sync_module_states,
     torch/nn/parallel/distributed.py:879-889) -- over torch.distributed (NCCL/gloo =
     bootstrap only), as is the exchange of the CUDA-IPC handles of the symmetric arenas;
-  * a post-accumulate-grad hook per parameter copies the fresh gradient into its slot of the
-    flat g arena (which IS the NVLink communication buffer -- no separate bucket copy as with
-    DDP's gradient_as_bucket_view=False) and frees the autograd allocation;
+  * gradients land in the flat g arena, which IS the NVLink communication buffer (no separate
+    bucket copy as with DDP's gradient_as_bucket_view=False): from a post-accumulate-grad hook per
+    parameter when the exchange overlaps backward, else by one multi-tensor copy in
+    optimizer.step() (no Python runs during backward); the autograd allocations are freed;
   * mode "replicated": buckets of the arena are all-reduced by K1 on a side stream as soon as
     all their gradients have landed (in bucket order, like the Reducer), overlapping the rest
     of backward; optimizer.step() then runs K2 over the whole arena on every rank;

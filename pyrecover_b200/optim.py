@@ -67,6 +67,10 @@ class B200AdamW(torch.optim.Optimizer):
         if self._grad_sync is not None:
             if self._arenas:
                 raise NotImplementedError("GradSync supports a single param group (as the reference uses)")
+            if self.max_grad_norm and self._grad_sync.mode == "overlap":
+                raise NotImplementedError("gradient clipping needs every gradient before the first update, but "
+                                          "'overlap' updates bucket by bucket under backward: use --grad-sync "
+                                          "fused or replicated with --clip-grad-norm")
             arena = FlatArena(params, world=self._grad_sync.world, alloc=self._grad_sync.alloc)
             self._grad_sync.attach(arena)
 
