@@ -441,3 +441,52 @@ def test_convert_reference_vanilla_to_dcp_and_back(tmp_path, golden_dir):
     assert again["step"] == 3 and all(torch.equal(again["model"][k], state["model"][k]) for k in state["model"])
     with pytest.raises(RuntimeError, match="neither"):
         convert.load_state_cpu(str(tmp_path))
+
+
+def test_convert_reads_a_sharded_directory_without_gpu(tmp_path):
+    """The sharded format is self-describing (shard_<r>.json pieces + the layout table in meta.pt):
+    a directory laid out by hand for world size 2, with the two ranks' runs interleaved, comes back
+    as the reference's state dict; a missing COMPLETE marker or a truncated shard is an error."""
+    from pyrecover import convert
+    w = torch.arange(96, dtype=torch.float32).reshape(8, 12).bfloat16()
+    b = torch.arange(8, dtype=torch.float32).bfloat16()
+    m = (torch.arange(96, dtype=torch.float32) * 0.5).reshape(8, 12).bfloat16()
+    v = (torch.arange(96, dtype=torch.float32) * 0.25).reshape(8, 12).bfloat16()
+    # image: w @0 (192 B) | b @256 (16 B) | m @512 | v @768 ; total 1024
+    image = np.zeros(1024, dtype=np.uint8)
+    for off, t in ((0, w), (256, b), (512, m), (768, v)):
+        raw = t.contiguous().view(torch.uint8).numpy().reshape(-1)
+        image[off:off + raw.size] = raw
+    d = tmp_path / "ckpt_9"
+    d.mkdir()
+    runs = {0: [(0, 96), (256, 16), (512, 96), (768, 96)], 1: [(96, 96), (608, 96), (864, 96)]}
+    for r, pieces in runs.items():
+        blob, table, loff = bytearray(), [], 0
+        for goff, n in pieces:
+            table.append([goff, n, loff])
+            blob += image[goff:goff + n].tobytes() + b"\0" * ((-n) % 256)
+            loff += n + ((-n) % 256)
+        (d / f"shard_{r:05d}.bin").write_bytes(bytes(blob))
+        (d / f"shard_{r:05d}.json").write_text(json.dumps({"format": 1, "rank": r, "world": 2, "sum64": [0, 0],
+                                                            "image_bytes": loff, "full_image_bytes": 1024, "pieces": table}))
+        (d / f"COMPLETE_{r:05d}").write_text("2")
+    layout = {"model": {"lin.weight": ["bfloat16", 0, [8, 12]], "lin.bias": ["bfloat16", 256, [8]]},
+              "optimizer": {0: {"exp_avg": ["bfloat16", 512, [8, 12]], "exp_avg_sq": ["bfloat16", 768, [8, 12]]}, 1: {}},
+              "image_bytes": 1024}
+    torch.save({"epoch": 2, "step": 9, "opt_steps": [9], "param_groups": [{"lr": 1e-3, "betas": (0.9, 0.999)}],
+                "lr_scheduler": {"last_epoch": 9}, "layout": layout}, d / "meta.pt")
+    st = convert.load_state_cpu(str(d))
+    assert st["epoch"] == 2 and st["step"] == 9 and list(st["model"]) == ["lin.weight", "lin.bias"]
+    assert torch.equal(st["model"]["lin.weight"], w) and torch.equal(st["model"]["lin.bias"], b)
+    assert torch.equal(st["optimizer"]["state"][0]["exp_avg"], m) and torch.equal(st["optimizer"]["state"][0]["exp_avg_sq"], v)
+    assert float(st["optimizer"]["state"][0]["step"]) == 9.0 and 1 not in st["optimizer"]["state"]
+    assert st["optimizer"]["param_groups"][0]["params"] == [0, 1] and st["lr_scheduler"] == {"last_epoch": 9}
+    out = tmp_path / "v.pt"
+    assert convert.main([str(d), str(out), "--to", "vanilla"]) == 0
+    assert torch.equal(torch.load(out, map_location="cpu", weights_only=False)["model"]["lin.weight"], w)
+    (d / "shard_00001.bin").write_bytes((d / "shard_00001.bin").read_bytes()[:300])
+    with pytest.raises(RuntimeError, match="truncated"):
+        convert.load_state_cpu(str(d))
+    (d / "COMPLETE_00001").unlink()
+    with pytest.raises(RuntimeError, match="incomplete"):
+        convert.load_state_cpu(str(d))
