@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define PR_ABI_VERSION 2
+#define PR_ABI_VERSION 3
 #define PR_MAX_WORLD 8            /* one NVSwitch domain: 8 x B200                          */
 #define PR_MAX_REGIONS 4          /* symmetric regions per communicator                     */
 #define PR_EXPORT_BLOB_BYTES 512  /* bytes pr_comm_export writes per rank                   */
@@ -88,13 +88,27 @@ int pr_adamw_plan_destroy(pr_adamw_plan *plan);
 int pr_adamw_scattered(const pr_adamw_plan *plan, void *p_dev, const void *const *grad_dev,
                        void *m_dev, void *v_dev, const pr_adamw_args *args, void *stream);
 
+/* Copy the gradients of tensors [seg_lo, seg_hi) of the plan from where autograd left them into the flat
+ * gradient arena g_dev (element offsets as in the plan) -- the Reducer's gradient -> bucket copy
+ * (torch/csrc/distributed/c10d/reducer.cpp, fired from loss.backward(), reference train.py:269), as one
+ * launch per bucket.  grad_dev has one entry per tensor of the plan; only [seg_lo, seg_hi) are read.
+ * max_blocks bounds the grid (0 = 3 CTAs per SM). */
+int pr_gather_grads(const pr_adamw_plan *plan, const void *const *grad_dev, int seg_lo, int seg_hi,
+                    void *g_dev, int max_blocks, void *stream);
+
 /* Global-norm gradient clipping -- the reference's clip_grad_norm_ (utils.py:84-89: total =
  * get_total_norm(grads), then clip_grads_with_norm_(params, max_norm, total)), whose call is
  * commented out at train.py:271-272 with the flag --grad-max-norm (utils.py:171-175) left behind.
  *   out_dev[0] = prescale * sqrt(sum g_i^2)                    (the total L2 norm)
  *   out_dev[1] = min(1, max_norm / (out_dev[0] + 1e-6))        (1 when max_norm <= 0)
- *   out_dev[2] = 1 if the norm is not finite, else 0           (the reference raises; check it lazily)
- * Pass out_dev + 1 as pr_adamw_args.grad_scale_dev and the update applies the coefficient in
+ *                and -1 when the norm is not finite: a negative (or NaN) device scale makes pr_adamw,
+ *                pr_adamw_scattered and pr_allreduce_adamw return without touching p, m or v
+ *   out_dev[2] = 1 if the norm is not finite, else 0
+ *   out_dev[3] += 1 when the norm is not finite (sticky; zero it once)
+ * The reference raises on a non-finite norm (utils.py:87, error_if_nonfinite=True) before the optimizer
+ * runs.  Here the host learns of it later (it reads out_dev[3] when it logs or saves), so the update is
+ * withheld on the device instead: inf/NaN gradients never reach the parameters, the moments or a checkpoint.
+ * out_dev holds 4 floats.  Pass out_dev + 1 as pr_adamw_args.grad_scale_dev and the update applies the coefficient in
  * fp32 inside K2 -- no extra pass over the gradients and no rounding of the clipped gradients to
  * bf16 as clip_grads_with_norm_ does.  Two launches; squares are summed in fp32 per thread, in
  * double across threads and CTAs, in a fixed order: the result is deterministic for a given n
@@ -143,6 +157,24 @@ int pr_ckpt_pack(const pr_pack_plan *plan, void *image, uint64_t *sum_dev, void 
 int pr_ckpt_unpack(const pr_pack_plan *plan, const void *image, uint64_t *sum_dev,
                    void *stream);
 
+/* The same two calls with the kernel and its grid chosen by the caller.
+ *   PR_PACK_BULK: the bytes move as bulk asynchronous copies staged through shared memory
+ *     (cp.async.bulk global -> shared -> global; one elected thread per CTA issues them, mbarriers track
+ *     them, the checksum is taken from the shared-memory tile) -- the north_star's "TMA-staged" pack.  A few
+ *     dozen CTAs carry it, so the snapshot that runs on a side stream beside the next forward pass
+ *     (reference: the save the training loop blocks on at train.py:310-340) takes few SMs, no registers
+ *     and no issue slots from it.  Needs every tensor base 16-byte aligned and the image in device memory.
+ *   PR_PACK_LDG: 16-byte loads / stores through registers on all SMs; any alignment, image may be mapped
+ *     pinned host memory.
+ *   PR_PACK_AUTO (what pr_ckpt_pack / pr_ckpt_unpack use): BULK when its two conditions hold, else LDG.
+ * max_blocks bounds the grid (0 = the kernel's default: PR_CKPT_BULK_BLOCKS or 64 CTAs for BULK, 3 CTAs
+ * per SM for LDG).  Results (image bytes, tensors, PR-SUM64) are identical whichever kernel runs. */
+typedef enum pr_pack_algo { PR_PACK_AUTO = 0, PR_PACK_LDG = 1, PR_PACK_BULK = 2 } pr_pack_algo;
+int pr_ckpt_pack_ex(const pr_pack_plan *plan, void *image, uint64_t *sum_dev, int algo, int max_blocks,
+                    void *stream);
+int pr_ckpt_unpack_ex(const pr_pack_plan *plan, const void *image, uint64_t *sum_dev, int algo,
+                      int max_blocks, void *stream);
+
 /* pr_ckpt_pack for callers that must not allocate.  (No counterpart in the reference: its
  * save path allocates freely.)  A checkpoint matters most when it is hardest to take: in the
  * walltime / preemption handler of a job that has filled HBM, where the cudaMalloc behind
@@ -152,8 +184,10 @@ int pr_ckpt_unpack(const pr_pack_plan *plan, const void *image, uint64_t *sum_de
  * cudaFree or other allocating call; the caller still supplies the tensors, the image and sum_dev.
  *   Limits: n <= 1024 tensors and at most 65536 tiles of 64 KiB (4 GiB of payload when tensors
  *   are tile multiples); beyond either the call fails with PR_ERR_INVALID and says so.
- *   First call on a device resolves the array's device address (that device must be current);
- *   make that first call before any stream capture begins.
+ *   Every call resolves the array's device address for the current device.  The FIRST call on a device
+ *   is also what loads the kernel image and materialises the 288 KiB array there (CUDA loads modules
+ *   lazily): make one small warm-up call per device at start-up -- before memory fills, and before any
+ *   stream capture begins -- so that the call that matters later finds everything in place.
  *   All calls share the one array and it keeps the previous call's table; each call rewrites every
  *   entry it reads, so nothing needs clearing -- but two calls whose GPU work overlaps (different
  *   streams, or threads racing on one device) would overwrite each other's table: serialise them.
@@ -221,6 +255,32 @@ int pr_comm_error(pr_comm *comm, int *timed_out);
  * *in_use: PR_AR_AUTO, pr_allreduce_adamw and pr_allgather_slices take the multicast kernels.
  * Every rank must choose the same policy.  Either out pointer may be NULL. */
 int pr_comm_multicast(pr_comm *comm, int policy, int *available, int *in_use);
+
+/* A barrier that times out (PR_COMM_TIMEOUT_S, default 20 s: a peer died or is stuck) makes the kernel
+ * return BEFORE it reads or writes any gradient, parameter or moment, raises the error word that
+ * pr_comm_error reports and tells every peer to give up as well; the communicator refuses further work
+ * (PR_ERR_STATE).  State that a late peer might have half-written is never consumed.
+ *
+ * Statistics of the kernels launched on this communicator so far (read with a synchronising copy: call
+ * it outside the training loop): out3[0] = nanoseconds CTA 0 spent in the begin barrier waiting for the
+ * slowest rank, out3[1] = launches, out3[2] = nanoseconds CTA 0 ran in total.  Separates rank skew from
+ * transfer time.  reset != 0 zeroes the counters. */
+int pr_comm_stats(pr_comm *comm, uint64_t *out3, int reset);
+
+/* One word from rank 0 to every rank without a collective of its own and without a host synchronisation:
+ * the job of the per-step `dist.broadcast(should_stop)` + `.item()` of reference train.py:342-346.
+ * pr_comm_signal_post (rank 0; other ranks' posts are ignored) enqueues a store of `value` into rank 0's
+ * signal word on `stream`.  The begin barrier of every later collective of this communicator reads it on
+ * every rank and drops (launch sequence number << 32 | value) into a host-mapped word;
+ * pr_comm_signal_read returns that pair without touching the GPU.  pr_comm_seq is the sequence number of
+ * the most recent launch: a value read with seq_out >= the pr_comm_seq noted after some step's exchange
+ * was posted no later than that step. */
+int pr_comm_signal_post(pr_comm *comm, uint32_t value, void *stream);
+int pr_comm_signal_read(pr_comm *comm, uint32_t *seq_out, uint32_t *value_out);
+int pr_comm_seq(pr_comm *comm, uint32_t *seq_out);
+/* Test aid (emulated communicators only): rank `rank` never reaches a barrier, as if its process had
+ * died; -1 = everybody present. */
+int pr_comm_test_absent_rank(pr_comm *comm, int rank);
 
 typedef enum pr_ar_algo {
     PR_AR_AUTO = 0,       /* one-shot <= 512 KiB, else multimem when pr_comm_multicast says in_use, else two-shot */

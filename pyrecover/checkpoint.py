@@ -21,6 +21,7 @@ from __future__ import annotations
 import hashlib
 import os
 import threading
+import weakref
 from pathlib import Path
 from typing import Any, Dict, Optional, Tuple
 
@@ -28,7 +29,9 @@ import torch
 import torch.distributed as dist
 
 _MD5_CHUNK = 64 << 20
-_SNAPSHOTTERS: Dict[int, Any] = {}
+# one snapshot engine per live optimizer; keyed by a weak reference (an id() may be reused by a later
+# object once the optimizer is gone, and the entry must not keep the arenas alive)
+_SNAPSHOTTERS: "weakref.WeakKeyDictionary[Any, Any]" = weakref.WeakKeyDictionary()
 
 
 # ------------------------------------------------------------------------- helpers --------
@@ -46,11 +49,10 @@ def _is_b200(optimizer) -> bool:
 
 def _snapshotter(model, optimizer):
     from pyrecover_b200.snapshot import Snapshotter
-    key = id(optimizer)
-    snap = _SNAPSHOTTERS.get(key)
-    if snap is None or snap.optimizer is not optimizer:
+    snap = _SNAPSHOTTERS.get(optimizer)
+    if snap is None:
         snap = Snapshotter(model, optimizer)
-        _SNAPSHOTTERS[key] = snap
+        _SNAPSHOTTERS[optimizer] = snap
     return snap
 
 
@@ -61,30 +63,47 @@ def wait_for_checkpoints() -> None:
         snap.wait()
 
 
+def take_durable_checkpoint_time() -> Optional[float]:
+    """Seconds the most recently FINISHED asynchronous checkpoint took from the save call to the renamed
+    file -- reported once per write, None when no write has finished since the last call; never blocks.
+    This, not the milliseconds a save_* call takes to enqueue the snapshot, is what the time-aware
+    policy has to learn from (reference train.py:334-337 times its synchronous save)."""
+    best = None
+    for snap in list(_SNAPSHOTTERS.values()):
+        t = snap.take_durable_time()
+        if t is not None and (best is None or t > best):
+            best = t
+    return best
+
+
 def release_checkpoint_engines() -> None:
     """Free staging buffers / pinned arenas (called from dist_utils.maybe_cleanup_distributed)."""
-    for key in list(_SNAPSHOTTERS):
-        _SNAPSHOTTERS.pop(key).close()
-
-
-_RENDEZVOUS: Dict[str, torch.Tensor] = {}
+    for opt in list(_SNAPSHOTTERS.keys()):
+        snap = _SNAPSHOTTERS.pop(opt, None)
+        if snap is not None:
+            snap.close()
 
 
 def _save_barrier(fast: bool) -> None:
     """The barrier the reference places before and after a save (pyrecover/checkpoint.py:56,103).
-    Host path: dist.barrier(), as the reference.  B200 path: the save is asynchronous, so what the
-    barrier has to order is the GPU work, not the host -- a one-element allreduce enqueued on the
-    training stream makes every rank's stream wait for every other rank's without the
-    cudaDeviceSynchronize inside dist.barrier(), which would drain the launch queue of a loop
-    that is close to launch-bound (measured: ~4 ms of GPU idle per checkpoint)."""
-    if not fast or dist.get_backend() != "nccl":
+    Host path: dist.barrier(), as the reference.  B200 path: nothing.  The save is asynchronous and
+    stream-ordered after this rank's own optimizer step; what every rank writes is state that is
+    identical on all of them (replicated) or its own slice of it (sharded), and the steps themselves
+    are kept in lock-step by the begin/end barriers inside every K1 launch -- a second rendezvous
+    would only import the slowest rank's skew into everybody's training stream (measured in round 1:
+    up to 10 ms per checkpoint at 8 GPUs)."""
+    if not fast:
         dist.barrier()
-        return
-    dev = torch.device("cuda", torch.cuda.current_device())
-    tok = _RENDEZVOUS.get(str(dev))
-    if tok is None:
-        tok = _RENDEZVOUS[str(dev)] = torch.zeros(1, device=dev)
-    dist.all_reduce(tok)
+
+
+def _pre_save_checks(optimizer) -> None:
+    """B200 path: never publish state that a failed step may have touched."""
+    check = getattr(optimizer, "check_finite", None)
+    if check is not None:
+        check()
+    gs = getattr(optimizer, "_grad_sync", None)
+    if gs is not None and gs.comm.timed_out():
+        raise RuntimeError("refusing to write a checkpoint: the gradient exchange timed out waiting for a peer")
 
 
 def _rng_state() -> Dict[str, torch.Tensor]:
@@ -147,13 +166,17 @@ def save_ckpt_vanilla(
     fast = _is_b200(optimizer)
     if is_distributed:
         _save_barrier(fast)
-    if fast and getattr(optimizer, "_grad_sync", None) is not None:
-        optimizer._grad_sync.replicate_moments()          # collective: every rank takes part
+    if fast:
+        _pre_save_checks(optimizer)
+        if getattr(optimizer, "_grad_sync", None) is not None:
+            optimizer._grad_sync.replicate_moments()      # collective: every rank takes part
     if rank == 0 or not is_distributed:
-        state = _collect_state(model, optimizer, lr_scheduler, sampler, step, epoch)
         if fast:
-            _snapshotter(model, optimizer).save_vanilla(str(checkpoint_path), state, verify, max_keep)
+            snap = _snapshotter(model, optimizer)
+            dyn = snap.dynamic_state(lr_scheduler, sampler, step, epoch, _rng_state())
+            snap.save_vanilla(str(checkpoint_path), dyn, verify, max_keep)
         else:
+            state = _collect_state(model, optimizer, lr_scheduler, sampler, step, epoch)
             _host_save_vanilla(state, str(checkpoint_path), verify, max_keep)
     if is_distributed:
         _save_barrier(fast)
@@ -254,6 +277,7 @@ def save_ckpt_distributed(
         _save_barrier(fast)
     os.makedirs(os.path.dirname(str(checkpoint_path)) or ".", exist_ok=True)
     if fast:
+        _pre_save_checks(optimizer)
         world = dist.get_world_size() if is_distributed else 1
         groups = [{k: v for k, v in g.items() if k != "params"} for g in optimizer.param_groups]
         small = {"epoch": epoch, "step": step, "param_groups": groups,

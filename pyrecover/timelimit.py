@@ -44,10 +44,13 @@ class TimeAwarePolicy:
         self.buffer_time = INITIAL_ITER_MULT * self.max_iter_time + INITIAL_CKPT_MULT * self.max_ckpt_time
         self.end_time = job_end_time() if end_time is None else end_time
         self.clock = clock
+        # iterations that still run after the decision (the B200 path delivers rank 0's decision inside the
+        # gradient exchange, a fixed number of steps later, instead of a per-step broadcast + host sync)
+        self.extra_iterations = 0
 
     @property
     def threshold(self) -> float:
-        return self.max_iter_time + self.max_ckpt_time + self.buffer_time
+        return (1 + self.extra_iterations) * self.max_iter_time + self.max_ckpt_time + self.buffer_time
 
     def time_left(self) -> Optional[float]:
         return None if self.end_time is None else self.end_time - self.clock()

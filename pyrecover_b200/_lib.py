@@ -15,7 +15,8 @@ LIB_PATH = PKG_DIR / "libpyrecover_b200.so"
 
 PR_BF16, PR_F32 = 0, 1
 PR_AR_AUTO, PR_AR_ONE_SHOT, PR_AR_TWO_SHOT, PR_AR_MULTIMEM = 0, 1, 2, 3
-PR_ABI_VERSION = 2
+PR_ABI_VERSION = 3
+PR_PACK_AUTO, PR_PACK_LDG, PR_PACK_BULK = 0, 1, 2
 PR_GRAD_NORM_SCRATCH = 2048
 PR_MAX_WORLD = 8
 PR_MAX_REGIONS = 4
@@ -40,6 +41,7 @@ _SIGNATURES = {
     "pr_adamw_plan_create": (c_int, [c_void_p, c_void_p, c_int, c_uint64, POINTER(c_void_p)]),
     "pr_adamw_plan_destroy": (c_int, [c_void_p]),
     "pr_adamw_scattered": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, POINTER(AdamWArgs), c_void_p]),
+    "pr_gather_grads": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_void_p]),
     "pr_grad_norm": (c_int, [c_void_p, c_uint64, c_int, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "pr_grad_norm_scattered": (c_int, [c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p, c_void_p]),
     "pr_checksum": (c_int, [c_void_p, c_uint64, c_uint64, c_void_p, c_void_p]),
@@ -47,6 +49,8 @@ _SIGNATURES = {
     "pr_pack_plan_destroy": (c_int, [c_void_p]),
     "pr_ckpt_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
     "pr_ckpt_unpack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p]),
+    "pr_ckpt_pack_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "pr_ckpt_unpack_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "pr_ckpt_pack_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_uint64, c_void_p, c_void_p]),
     "pr_host_arena_alloc": (c_int, [c_uint64, POINTER(c_void_p)]),
     "pr_host_arena_free": (c_int, [c_void_p]),
@@ -63,6 +67,11 @@ _SIGNATURES = {
     "pr_comm_import": (c_int, [c_void_p, c_void_p]),
     "pr_comm_error": (c_int, [c_void_p, POINTER(c_int)]),
     "pr_comm_multicast": (c_int, [c_void_p, c_int, POINTER(c_int), POINTER(c_int)]),
+    "pr_comm_stats": (c_int, [c_void_p, c_void_p, c_int]),
+    "pr_comm_signal_post": (c_int, [c_void_p, ctypes.c_uint32, c_void_p]),
+    "pr_comm_signal_read": (c_int, [c_void_p, POINTER(ctypes.c_uint32), POINTER(ctypes.c_uint32)]),
+    "pr_comm_seq": (c_int, [c_void_p, POINTER(ctypes.c_uint32)]),
+    "pr_comm_test_absent_rank": (c_int, [c_void_p, c_int]),
     "pr_allreduce": (c_int, [c_void_p, c_int, c_uint64, c_uint64, c_int, c_float, c_int, c_int, c_void_p]),
     "pr_allreduce_adamw": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_uint64, c_uint64, c_int,
                                    POINTER(AdamWArgs), c_int, c_void_p]),

@@ -54,6 +54,7 @@ __global__ void __launch_bounds__(kThreads, kMinBlocks)
 adamw_bf16_kernel(uint4 *__restrict__ p, const void *__restrict__ g_, uint4 *__restrict__ m,
                   uint4 *__restrict__ v, uint64_t nvec, AdamWConsts c_) {
     const AdamWConsts c = resolve_gscale(c_);
+    if (c.skip) return;
     const AdamWFast f = make_adamw_fast(c);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
@@ -93,6 +94,7 @@ __global__ void __launch_bounds__(kThreads)
 adamw_f32_kernel(float4 *__restrict__ p, const float4 *__restrict__ g, float4 *__restrict__ m,
                  float4 *__restrict__ v, uint64_t nvec, AdamWConsts c_) {
     const AdamWConsts c = resolve_gscale(c_);
+    if (c.skip) return;
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     for (uint64_t i = (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < nvec; i += stride) {
         float4 P = p[i], G = __ldg(g + i), M = m[i], V = v[i];
@@ -109,6 +111,7 @@ template <int NUMERICS>
 __global__ void adamw_scalar_kernel(void *p_, const void *g_, void *m_, void *v_, uint64_t first,
                                     uint64_t n, int dtype, int grad_dtype, AdamWConsts c_) {
     const AdamWConsts c = resolve_gscale(c_);
+    if (c.skip) return;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = first + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
         if (dtype == PR_F32) {
@@ -156,6 +159,7 @@ adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, 
                             AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
                             const __grid_constant__ GradPtrs gp, AdamWConsts c_) {
     const AdamWConsts c = resolve_gscale(c_);
+    if (c.skip) return;
     const AdamWFast f = make_adamw_fast(c);
     for (uint64_t t = tile_lo + blockIdx.x; t < tile_hi; t += gridDim.x) {
         const uint32_t s = pd.tile_seg[t];
@@ -198,6 +202,37 @@ adamw_bf16_scattered_kernel(uint16_t *__restrict__ p, uint16_t *__restrict__ m, 
             else adamw_fp32(pf, g, mf, vf, c);
             p[i] = (uint16_t)f2bf_bits(pf); m[i] = (uint16_t)f2bf_bits(mf); v[i] = (uint16_t)f2bf_bits(vf);
         }
+    }
+}
+
+// ---- gather: gradients from where autograd left them into the flat g arena ----------------------
+// With W > 1 the gradient exchange needs the gradients in the symmetric (peer-mapped, multicast-bound)
+// arena.  This is that copy, as ONE launch per bucket of tensors [seg_lo, seg_hi) over the same tile
+// table as the scattered K2 -- instead of a library multi-tensor copy of all 147-291 tensors after
+// backward has finished (reference: the Reducer's grad -> bucket copy, torch/csrc/distributed/c10d/
+// reducer.cpp mark_variable_ready_dense; call site train.py:269).  HBM: 2 B read + 2 B write per element.
+__global__ void __launch_bounds__(kThreads)
+gather_grads_kernel(uint16_t *__restrict__ g, AdamWPlanDev pd, uint64_t tile_lo, uint64_t tile_hi, uint32_t seg_lo,
+                    const __grid_constant__ GradPtrs gp) {
+    for (uint64_t t = tile_lo + blockIdx.x; t < tile_hi; t += gridDim.x) {
+        const uint32_t s = pd.tile_seg[t];
+        const uint64_t off = (t - pd.tile_first[s]) * kTileElems;
+        const uint64_t left = pd.numel[s] - off;
+        const uint32_t n = left < kTileElems ? (uint32_t)left : kTileElems;
+        const uint64_t base = pd.elem_off[s] + off;
+        const uint16_t *src = reinterpret_cast<const uint16_t *>(gp.ptr[s - seg_lo]) + off;
+        const uint4 *S = reinterpret_cast<const uint4 *>(src);
+        uint4 *D = reinterpret_cast<uint4 *>(g + base);
+        const uint32_t nvec = n / 8;
+        uint32_t k = threadIdx.x;
+        for (; k + 3 * kThreads < nvec; k += 4 * kThreads) {
+            uint4 a = ld_stream_nc(S + k), b = ld_stream_nc(S + k + kThreads), c = ld_stream_nc(S + k + 2 * kThreads),
+                  d = ld_stream_nc(S + k + 3 * kThreads);
+            st_stream(D + k, a); st_stream(D + k + kThreads, b); st_stream(D + k + 2 * kThreads, c);
+            st_stream(D + k + 3 * kThreads, d);
+        }
+        for (; k < nvec; k += kThreads) st_stream(D + k, ld_stream_nc(S + k));
+        if (threadIdx.x < (n & 7u)) g[base + 8ull * nvec + threadIdx.x] = src[8u * nvec + threadIdx.x];
     }
 }
 
@@ -329,8 +364,9 @@ norm_finish_kernel(double *__restrict__ partial, int count, float prescale, floa
                 if (coef > 1.0f) coef = 1.0f;
             }
             out[0] = norm;
-            out[1] = coef;
+            out[1] = finite ? coef : -1.0f;      // negative: K2 leaves p, m, v untouched (resolve_gscale)
             out[2] = finite ? 0.0f : 1.0f;
+            if (!finite) out[3] = out[3] + 1.0f; // sticky count of non-finite norms (the host checks it lazily)
         }
     }
 }
@@ -542,6 +578,32 @@ extern "C" int pr_grad_norm_scattered(const pr_adamw_plan *plan, const void *con
                                                            hi == plan->n ? 1 : 0);
         PR_CUDA(cudaGetLastError());
         pr_count_launch(2);
+    }
+    return PR_OK;
+}
+
+extern "C" int pr_gather_grads(const pr_adamw_plan *plan, const void *const *grad_dev, int seg_lo, int seg_hi,
+                               void *g_dev, int max_blocks, void *stream_) {
+    PR_REQUIRE(plan && grad_dev && g_dev, "pr_gather_grads: NULL argument");
+    PR_REQUIRE(seg_lo >= 0 && seg_lo <= seg_hi && seg_hi <= plan->n, "pr_gather_grads: tensor range [%d, %d) not in [0, %d]",
+               seg_lo, seg_hi, plan->n);
+    PR_REQUIRE(pr_aligned16(g_dev), "pr_gather_grads: the arena must be 16-B aligned");
+    for (int i = seg_lo; i < seg_hi; ++i)
+        PR_REQUIRE(grad_dev[i] != nullptr && pr_aligned16(grad_dev[i]), "pr_gather_grads: gradient %d is NULL or not 16-B aligned", i);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    for (int s0 = seg_lo; s0 < seg_hi; s0 += kMaxGradPtrs) {
+        const int s1 = s0 + kMaxGradPtrs < seg_hi ? s0 + kMaxGradPtrs : seg_hi;
+        GradPtrs gp;
+        memset(&gp, 0, sizeof(gp));
+        for (int s = s0; s < s1; ++s) gp.ptr[s - s0] = grad_dev[s];
+        const uint64_t t0 = plan->tile_first[s0], t1 = plan->tile_first[s1];
+        if (t1 == t0) continue;
+        uint64_t cap = (uint64_t)pr_sm_count() * kDefaultBlocksPerSM;
+        if (max_blocks > 0 && (uint64_t)max_blocks < cap) cap = (uint64_t)max_blocks;
+        int grid = (int)((t1 - t0) < cap ? (t1 - t0) : cap);
+        gather_grads_kernel<<<grid, kThreads, 0, stream>>>((uint16_t *)g_dev, plan->dev, t0, t1, (uint32_t)s0, gp);
+        PR_CUDA(cudaGetLastError());
+        pr_count_launch();
     }
     return PR_OK;
 }

@@ -56,7 +56,10 @@ constexpr int kSlots = 2;
 constexpr int kMulticastBlocksSmall = 16, kMulticastBlocksLarge = 32;
 constexpr uint64_t kMulticastLargeBytes = 1ull << 30;
 constexpr int kOneShotVecPerThread = 4;  // register budget of the one-shot kernel
-constexpr size_t kFlagWords = (size_t)kSlots * kMaxBlocks * PR_MAX_WORLD;
+constexpr size_t kBarrierWords = (size_t)kSlots * kMaxBlocks * PR_MAX_WORLD;
+constexpr size_t kAbortWord = kBarrierWords;          // set by a peer whose barrier timed out: everybody gives up
+constexpr size_t kSignalWord = kBarrierWords + 1;     // a rank's posted signal (pr_comm_signal_post), read by every peer
+constexpr size_t kFlagWords = kBarrierWords + 64;
 constexpr uint32_t kBlobMagic = 0x50523142u;  // "PR1B"
 
 struct CommDev {
@@ -66,6 +69,9 @@ struct CommDev {
     uint32_t seq;
     unsigned long long timeout_ns;
     int *err;                        // mapped host word: set to 1 when a barrier timed out
+    int absent_rank;                 // emulated communicators only (tests): this rank never shows up; -1 = none
+    unsigned long long *stats;       // device: [0] ns CTA 0 waited at the begin barrier, [1] launches, [2] ns CTA 0 ran
+    unsigned long long *signal_host; // mapped host word: (launch sequence << 32) | rank 0's posted signal
     uint8_t *grad[PR_MAX_WORLD];     // region base on rank i as mapped here
     uint8_t *param[PR_MAX_WORLD];    // second region (fused kernel pushes parameters)
     uint8_t *mom1[PR_MAX_WORLD];     // exp_avg region (fused kernel; only the own rank's is touched)
@@ -83,28 +89,73 @@ __device__ __forceinline__ unsigned long long globaltimer() {
 
 __device__ __forceinline__ int my_rank(const CommDev &c) { return c.emulated ? (int)blockIdx.y : c.rank; }
 
-// CTA blockIdx.x of all ranks rendezvous.  On timeout the error word is raised and the CTA
-// carries on (results are then garbage, but the GPU is not left hanging).
-__device__ __forceinline__ void xbarrier(const CommDev &c, int rank, int slot) {
+// CTA blockIdx.x of all ranks rendezvous.  Returns false when a peer did not show up within the
+// timeout (or a peer already gave up): the error word is raised, every peer's abort word is set so
+// that nobody else waits out its own timeout, and the caller must return WITHOUT touching any data
+// -- a rank that reads gradients a peer never finished writing, updates its parameters from them and
+// pushes the result into every peer's arena has destroyed the job's state by the time the host finds
+// out.  The verdict is uniform over the CTA.
+__device__ __forceinline__ bool xbarrier(const CommDev &c, int rank, int slot) {
     __syncthreads();
+    int failed = 0;
     if ((int)threadIdx.x < c.world) {
         const int peer = threadIdx.x;
         const size_t idx = ((size_t)slot * kMaxBlocks + blockIdx.x) * PR_MAX_WORLD;
         __threadfence_system();
         st_release_sys(c.flags[peer] + idx + rank, c.seq);
         const uint32_t *mine = c.flags[rank] + idx + peer;
+        const uint32_t *abort_word = c.flags[rank] + kAbortWord;
         unsigned long long t0 = 0;
         uint32_t spins = 0;
         while ((int32_t)(ld_acquire_sys(mine) - c.seq) < 0) {
             if ((++spins & 0x3ffu) == 0) {
                 unsigned long long now = globaltimer();
                 if (t0 == 0) t0 = now;
-                else if (now - t0 > c.timeout_ns) { *c.err = 1; break; }
+                else if (now - t0 > c.timeout_ns || ld_acquire_sys(abort_word) != 0) { failed = 1; break; }
             }
         }
     }
-    __syncthreads();
+    failed = __syncthreads_or(failed);
+    if (failed && (int)threadIdx.x < c.world) {
+        if (threadIdx.x == 0) *c.err = 1;
+        st_release_sys(c.flags[threadIdx.x] + kAbortWord, 1u);
+    }
+    return failed == 0;
 }
+
+// Begin barrier of every K1 kernel.  Besides the rendezvous: an emulated rank marked absent leaves
+// at once (tests of the timeout path); CTA 0 adds the time it waited for the slowest peer to the
+// communicator's statistics and forwards rank 0's signal word to this rank's host.
+struct KernelClock { unsigned long long t_start; };
+
+__device__ __forceinline__ bool k1_begin(const CommDev &c, int rank, KernelClock &clk) {
+    if (c.emulated && c.absent_rank == rank) return false;
+    const bool lead = blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0;   // one clock per launch (emulated: rank 0's CTA 0)
+    if (lead) clk.t_start = globaltimer();
+    int dead = 0;
+    if (threadIdx.x == 0) dead = ld_acquire_sys(c.flags[rank] + kAbortWord) != 0;      // a peer gave up earlier
+    if (__syncthreads_or(dead)) {
+        if (threadIdx.x == 0) *c.err = 1;
+        return false;
+    }
+    const bool ok = xbarrier(c, rank, 0);
+    if (lead) {
+        atomicAdd(c.stats + 0, globaltimer() - clk.t_start);
+        atomicAdd(c.stats + 1, 1ull);
+        if (ok && c.signal_host != nullptr) {
+            const uint32_t sig = ld_acquire_sys(c.flags[0] + kSignalWord);
+            *reinterpret_cast<volatile unsigned long long *>(c.signal_host) = ((unsigned long long)c.seq << 32) | sig;
+        }
+    }
+    return ok;
+}
+
+__device__ __forceinline__ void k1_end(const CommDev &c, int rank, const KernelClock &clk) {
+    xbarrier(c, rank, 1);
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicAdd(c.stats + 2, globaltimer() - clk.t_start);
+}
+
+__global__ void signal_post_kernel(uint32_t *word, uint32_t value) { st_release_sys(word, value); }
 
 // ---- element helpers ------------------------------------------------------------------
 template <bool F32> struct Acc;
@@ -160,7 +211,8 @@ template <int W, bool F32>
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_twoshot_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
     const int rank = my_rank(c);
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, W, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
@@ -189,7 +241,7 @@ allreduce_twoshot_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
             }
         }
     }
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 // ---- one-shot (every rank reads everything; small messages) -------------------------------
@@ -197,7 +249,8 @@ template <int W, bool F32>
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_oneshot_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
     const int rank = my_rank(c);
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     const uint64_t i0 = (uint64_t)blockIdx.x * kThreads + threadIdx.x;
     uint4 res[kOneShotVecPerThread];
@@ -215,12 +268,13 @@ allreduce_oneshot_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
             res[k] = acc.finish(scale);
         }
     }
-    xbarrier(c, rank, 1);   // every rank has finished reading: the buffers may be overwritten
+    if (!xbarrier(c, rank, 1)) return;   // every rank has finished reading: the buffers may be overwritten
 #pragma unroll
     for (int k = 0; k < kOneShotVecPerThread; ++k) {
         const uint64_t j = i0 + k * stride;
         if (j < nvec) st_stream(c.grad[rank] + off + 16 * j, res[k]);
     }
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) atomicAdd(c.stats + 2, globaltimer() - clk.t_start);
 }
 
 // ---- fused reduce-scatter -> AdamW -> parameter all-gather (bf16) ----------------------------
@@ -228,12 +282,14 @@ template <int W>
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac_) {
     const AdamWConsts ac = resolve_gscale(ac_);
+    if (ac.skip) return;      // uniform over CTAs and ranks: nobody reaches the barrier
     const int rank = my_rank(c);
     const uint64_t poff = goff;
     uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
     uint4 *__restrict__ v = reinterpret_cast<uint4 *>(c.mom2[rank] + goff);
     const AdamWFast fast = make_adamw_fast(ac);
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, W, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
@@ -253,7 +309,7 @@ allreduce_adamw_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac_)
 #pragma unroll
         for (int r = 0; r < W; ++r) st_stream(c.param[r] + poff + 16 * i, P);
     }
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 // ---- all-gather of per-rank slices (push) ----------------------------------------------------
@@ -261,7 +317,8 @@ template <int W>
 __global__ void __launch_bounds__(kThreads, 1)
 allgather_slices_kernel(CommDev c, uint64_t off, uint64_t nvec) {
     const int rank = my_rank(c);
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, W, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
@@ -271,7 +328,7 @@ allgather_slices_kernel(CommDev c, uint64_t off, uint64_t nvec) {
         for (int r = 0; r < W; ++r)
             if (r != rank) st_stream(c.grad[r] + off + 16 * i, x);
     }
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 // ---- NVSwitch multicast kernels ------------------------------------------------------------------
@@ -311,7 +368,8 @@ template <bool F32>
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_mc_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
     const int rank = c.rank;
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, c.world, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
@@ -330,7 +388,7 @@ allreduce_mc_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
             if (j < hi) mm_st(base + 16 * j, scale == 1.0f ? v[u] : scale_vec<F32>(v[u], scale));
         }
     }
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 // fused: switch-reduced gradient slice -> AdamW on the local (p, m, v) slice -> multicast store of
@@ -338,6 +396,7 @@ allreduce_mc_kernel(CommDev c, uint64_t off, uint64_t nvec, float scale) {
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts ac_) {
     const AdamWConsts ac = resolve_gscale(ac_);
+    if (ac.skip) return;      // uniform over CTAs and ranks: nobody reaches the barrier
     const int rank = c.rank;
     const uint8_t *__restrict__ p = c.param[rank] + goff;
     uint4 *__restrict__ m = reinterpret_cast<uint4 *>(c.mom1[rank] + goff);
@@ -345,7 +404,8 @@ allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts a
     const uint8_t *mg = c.mc_grad + goff;
     uint8_t *mp = c.mc_param + goff;
     const AdamWFast fast = make_adamw_fast(ac);
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, c.world, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
@@ -380,20 +440,21 @@ allreduce_adamw_mc_kernel(CommDev c, uint64_t goff, uint64_t nvec, AdamWConsts a
             }
         }
     }
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 // all-gather of per-rank slices through the switch: one multicast store instead of W - 1 pushes
 __global__ void __launch_bounds__(kThreads, 1)
 allgather_slices_mc_kernel(CommDev c, uint64_t off, uint64_t nvec) {
     const int rank = c.rank;
-    xbarrier(c, rank, 0);
+    KernelClock clk;
+    if (!k1_begin(c, rank, clk)) return;
     uint64_t lo, hi;
     slice_bounds(nvec, c.world, rank, lo, hi);
     const uint64_t stride = (uint64_t)gridDim.x * kThreads;
     for (uint64_t i = lo + (uint64_t)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride)
         mm_st(c.mc_grad + off + 16 * i, ld_stream(c.grad[rank] + off + 16 * i));
-    xbarrier(c, rank, 1);
+    k1_end(c, rank, clk);
 }
 
 struct Blob {
@@ -424,6 +485,9 @@ struct pr_comm {
     bool emulated = false, imported = false;
     uint32_t seq = 0;
     int *err_host = nullptr, *err_dev = nullptr;
+    unsigned long long *signal_host = nullptr, *signal_dev = nullptr;   // mapped host word written by K1's begin barrier
+    unsigned long long *stats_dev = nullptr;                             // 4 x u64 device counters (CommDev::stats)
+    int absent_rank = -1;                                                // emulated only: test hook
     unsigned long long timeout_ns = 20ull * 1000000000ull;
     // [rank][region]; for a real comm only [self] is owned, the rest are IPC / VMM mappings
     uint8_t *region[PR_MAX_WORLD][PR_MAX_REGIONS] = {};
@@ -454,6 +518,9 @@ static int fill_dev(pr_comm *c, int grad_region, int param_region, CommDev &d, i
     d.seq = ++c->seq;
     d.timeout_ns = c->timeout_ns;
     d.err = c->err_dev;
+    d.absent_rank = c->absent_rank;
+    d.stats = c->stats_dev;
+    d.signal_host = c->signal_dev;
     for (int r = 0; r < PR_MAX_WORLD; ++r) {
         d.grad[r] = r < c->world ? c->region[r][grad_region] : nullptr;
         d.param[r] = (r < c->world && param_region >= 0) ? c->region[r][param_region] : nullptr;
@@ -506,6 +573,33 @@ static int launch(pr_comm *c, const void *kernel, int grid, cudaStream_t stream,
         default: pr_set_error("world %d unsupported", world); return PR_ERR_INVALID; \
     }
 
+static void comm_timeout_from_env(pr_comm *c) {
+    if (const char *e = getenv("PR_COMM_TIMEOUT_S")) {
+        double s = atof(e);
+        if (s > 0) c->timeout_ns = (unsigned long long)(s * 1e9);
+    }
+}
+
+// Host words, counters and flag blocks of a communicator.  Any failure is returned to the caller,
+// which destroys the half-built object (pr_comm_destroy copes with whatever is still NULL).
+static int comm_init_common(pr_comm *c) {
+    PR_CUDA(cudaGetDevice(&c->device));
+    PR_CUDA(cudaHostAlloc((void **)&c->err_host, sizeof(int), cudaHostAllocMapped));
+    *c->err_host = 0;
+    PR_CUDA(cudaHostGetDevicePointer((void **)&c->err_dev, c->err_host, 0));
+    PR_CUDA(cudaHostAlloc((void **)&c->signal_host, sizeof(unsigned long long), cudaHostAllocMapped));
+    *c->signal_host = 0;
+    PR_CUDA(cudaHostGetDevicePointer((void **)&c->signal_dev, c->signal_host, 0));
+    PR_CUDA(cudaMalloc((void **)&c->stats_dev, 4 * sizeof(unsigned long long)));
+    PR_CUDA(cudaMemset(c->stats_dev, 0, 4 * sizeof(unsigned long long)));
+    for (int r = 0; r < c->world; ++r) {
+        if (!c->emulated && r != c->rank) continue;
+        PR_CUDA(cudaMalloc((void **)&c->flags[r], kFlagWords * sizeof(uint32_t)));
+        PR_CUDA(cudaMemset(c->flags[r], 0, kFlagWords * sizeof(uint32_t)));
+    }
+    return PR_OK;
+}
+
 extern "C" int pr_comm_create(int rank, int world, pr_comm **out) {
     PR_REQUIRE(out != nullptr, "pr_comm_create: comm_out is NULL");
     *out = nullptr;
@@ -514,16 +608,11 @@ extern "C" int pr_comm_create(int rank, int world, pr_comm **out) {
     auto *c = new pr_comm();
     c->rank = rank;
     c->world = world;
-    if (const char *e = getenv("PR_COMM_TIMEOUT_S")) {
-        double s = atof(e);
-        if (s > 0) c->timeout_ns = (unsigned long long)(s * 1e9);
+    comm_timeout_from_env(c);
+    if (int rc = comm_init_common(c)) {
+        pr_comm_destroy(c);
+        return rc;
     }
-    PR_CUDA(cudaGetDevice(&c->device));
-    PR_CUDA(cudaHostAlloc((void **)&c->err_host, sizeof(int), cudaHostAllocMapped));
-    *c->err_host = 0;
-    PR_CUDA(cudaHostGetDevicePointer((void **)&c->err_dev, c->err_host, 0));
-    PR_CUDA(cudaMalloc((void **)&c->flags[rank], kFlagWords * sizeof(uint32_t)));
-    PR_CUDA(cudaMemset(c->flags[rank], 0, kFlagWords * sizeof(uint32_t)));
     // NVSwitch multicast needs the regions to be VMM allocations; PR_COMM_MULTICAST=0 keeps the
     // cudaMalloc + CUDA-IPC regions (P2P kernels only), =1 uses multicast whenever it is available,
     // unset = multicast from W = 4 up
@@ -551,13 +640,10 @@ extern "C" int pr_comm_create_emulated(int world, pr_comm **out) {
     c->world = world;
     c->emulated = true;
     c->timeout_ns = 5ull * 1000000000ull;
-    PR_CUDA(cudaGetDevice(&c->device));
-    PR_CUDA(cudaHostAlloc((void **)&c->err_host, sizeof(int), cudaHostAllocMapped));
-    *c->err_host = 0;
-    PR_CUDA(cudaHostGetDevicePointer((void **)&c->err_dev, c->err_host, 0));
-    for (int r = 0; r < world; ++r) {
-        PR_CUDA(cudaMalloc((void **)&c->flags[r], kFlagWords * sizeof(uint32_t)));
-        PR_CUDA(cudaMemset(c->flags[r], 0, kFlagWords * sizeof(uint32_t)));
+    comm_timeout_from_env(c);
+    if (int rc = comm_init_common(c)) {
+        pr_comm_destroy(c);
+        return rc;
     }
     *out = c;
     return PR_OK;
@@ -584,6 +670,8 @@ extern "C" int pr_comm_destroy(pr_comm *c) {
     }
     pr_sock_close(&c->sock);
     if (c->err_host) cudaFreeHost(c->err_host);
+    if (c->signal_host) cudaFreeHost(c->signal_host);
+    if (c->stats_dev) cudaFree(c->stats_dev);
     delete c;
     return PR_OK;
 }
@@ -880,5 +968,48 @@ extern "C" int pr_allgather_slices(pr_comm *c, int region, uint64_t offset, uint
 extern "C" int pr_comm_error(pr_comm *c, int *timed_out) {
     PR_REQUIRE(c && timed_out, "pr_comm_error: NULL argument");
     *timed_out = *c->err_host;
+    return PR_OK;
+}
+
+// ---- statistics, signal word, test hook ------------------------------------------------------------
+extern "C" int pr_comm_stats(pr_comm *c, uint64_t *out3, int reset) {
+    PR_REQUIRE(c && out3, "pr_comm_stats: NULL argument");
+    unsigned long long h[4] = {0, 0, 0, 0};
+    PR_CUDA(cudaMemcpy(h, c->stats_dev, sizeof(h), cudaMemcpyDeviceToHost));      // synchronises: call it off the hot loop
+    out3[0] = h[0];
+    out3[1] = h[1];
+    out3[2] = h[2];
+    if (reset) PR_CUDA(cudaMemset(c->stats_dev, 0, sizeof(h)));
+    return PR_OK;
+}
+
+extern "C" int pr_comm_signal_post(pr_comm *c, uint32_t value, void *stream_) {
+    PR_REQUIRE(c != nullptr, "pr_comm_signal_post: comm is NULL");
+    const int r = c->emulated ? 0 : c->rank;
+    PR_REQUIRE(c->flags[r] != nullptr, "pr_comm_signal_post: communicator has no flag block");
+    signal_post_kernel<<<1, 1, 0, (cudaStream_t)stream_>>>(c->flags[r] + kSignalWord, value);
+    PR_CUDA(cudaGetLastError());
+    pr_count_launch();
+    return PR_OK;
+}
+
+extern "C" int pr_comm_signal_read(pr_comm *c, uint32_t *seq_out, uint32_t *value_out) {
+    PR_REQUIRE(c && seq_out && value_out, "pr_comm_signal_read: NULL argument");
+    const unsigned long long w = *reinterpret_cast<volatile unsigned long long *>(c->signal_host);
+    *seq_out = (uint32_t)(w >> 32);
+    *value_out = (uint32_t)(w & 0xffffffffull);
+    return PR_OK;
+}
+
+extern "C" int pr_comm_seq(pr_comm *c, uint32_t *seq_out) {
+    PR_REQUIRE(c && seq_out, "pr_comm_seq: NULL argument");
+    *seq_out = c->seq;
+    return PR_OK;
+}
+
+extern "C" int pr_comm_test_absent_rank(pr_comm *c, int rank) {
+    PR_REQUIRE(c != nullptr && c->emulated, "pr_comm_test_absent_rank: only emulated communicators (a test aid)");
+    PR_REQUIRE(rank >= -1 && rank < c->world, "pr_comm_test_absent_rank: rank %d out of range", rank);
+    c->absent_rank = rank;
     return PR_OK;
 }

@@ -189,6 +189,178 @@ pack_kernel(PlanDev pd, uint8_t *image, uint64_t *sum) {
     if (WITH_SUM) block_sum_commit(A, B, sum);
 }
 
+// ---- bulk-copy pack / unpack: TMA-staged through shared memory -------------------------------
+// The same gather / scatter + PR-SUM64, but the bytes move as bulk asynchronous copies
+// (cp.async.bulk: global -> shared -> global, UBLKCP in SASS) issued by ONE elected thread per CTA and
+// tracked by mbarriers; no data passes through registers except for the checksum, which the other
+// threads take from the shared-memory tile while the copy engine of the SM already writes it out.
+// A handful of CTAs keep enough bytes in flight (kBulkStages x kBulkChunk = 192 KiB of shared memory
+// per CTA), which leaves the remaining SMs, their registers and issue slots to the forward pass this
+// kernel runs beside (north_star: "pack kernel ... via TMA-staged async copies on a side stream").
+//
+// Pipeline of one CTA over its chunks q = 0, 1, ... (a chunk = <= kBulkChunk bytes of one tile):
+//   load(q)  : mbarrier.arrive.expect_tx(full[q % S]) + cp.async.bulk g->s        (thread 0)
+//   wait(q)  : mbarrier.try_wait.parity(full[q % S])                              (all threads)
+//   store(q) : cp.async.bulk s->g + commit_group                                  (thread 0)
+//   sum(q)   : PR-SUM64 over the tile in shared memory                            (all threads)
+//   refill   : at the top of iteration q, stage (q-2) % S is reloaded with chunk q+S-2 once
+//              cp.async.bulk.wait_group.read 1 says store(q-2) has drained it and the CTA barrier says
+//              every thread has finished summing it.
+// Requires every tensor base to be 16-byte aligned (the plan checks); a tensor's last < 16 bytes
+// are moved by thread 0 with byte accesses, zero-padded in the image like the LDG kernel does.
+constexpr int kBulkThreads = 256;
+constexpr uint32_t kBulkChunk = 32 * 1024;
+constexpr int kBulkStages = 6;
+constexpr size_t kBulkSmemBytes = (size_t)kBulkStages * kBulkChunk + 8 * kBulkStages;
+static_assert(kTileBytes % kBulkChunk == 0, "a tile is a whole number of chunks");
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" :: "r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar, uint64_t pol) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(smem_addr(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_addr(bar)), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void *gdst, const void *smem_src, uint32_t bytes, uint64_t pol) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+                 :: "l"(gdst), "r"(smem_addr(smem_src)), "r"(bytes), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+struct BulkChunk {
+    uint8_t *tensor;       // first byte of the chunk in the tensor
+    uint64_t ioff;         // its offset in the image (multiple of 16)
+    uint32_t len;          // bytes (<= kBulkChunk); only a tensor's last chunk may not be a multiple of 16
+};
+
+// Walks the chunks of tiles blockIdx.x, blockIdx.x + gridDim.x, ...  The tile -> tensor table is only
+// consulted when a tile leaves the tensor the previous one was in (tensors are arenas of gigabytes).
+struct BulkCursor {
+    uint64_t t, first = 0, ntiles_seg = 0, ptr = 0, off = 0, bytes = 0;
+    uint32_t h = 0;
+    bool cached = false;
+    __device__ __forceinline__ explicit BulkCursor(uint64_t t0) : t(t0) {}
+    __device__ __forceinline__ bool next(const PlanDev &pd, BulkChunk &c) {
+        while (t < pd.ntiles) {
+            if (!cached || t < first || t >= first + ntiles_seg) {
+                const uint32_t s = pd.tile_seg[t];
+                first = pd.tile_first[s];
+                ptr = pd.seg_ptr[s];
+                off = pd.seg_off[s];
+                bytes = pd.seg_bytes[s];
+                ntiles_seg = (bytes + kTileBytes - 1) / kTileBytes;
+                cached = true;
+            }
+            const uint64_t toff = (t - first) * kTileBytes + (uint64_t)h * kBulkChunk;
+            const bool exists = toff < bytes;
+            if (exists) {
+                const uint64_t left = bytes - toff;
+                c.tensor = reinterpret_cast<uint8_t *>(ptr) + toff;
+                c.ioff = off + toff;
+                c.len = left < kBulkChunk ? (uint32_t)left : kBulkChunk;
+            }
+            if (exists && h + 1 < kTileBytes / kBulkChunk && toff + kBulkChunk < bytes) {
+                ++h;
+            } else {
+                h = 0;
+                t += gridDim.x;
+            }
+            if (exists) return true;
+        }
+        return false;
+    }
+};
+
+template <bool UNPACK, bool WITH_SUM>
+__global__ void __launch_bounds__(kBulkThreads, 1)
+pack_bulk_kernel(PlanDev pd, uint8_t *image, uint64_t *sum) {
+    extern __shared__ __align__(128) uint8_t bulk_smem[];
+    uint64_t *full = reinterpret_cast<uint64_t *>(bulk_smem + (size_t)kBulkStages * kBulkChunk);
+    const bool leader = threadIdx.x == 0;
+    if (!WITH_SUM && !leader) return;            // without a checksum the elected thread does everything
+    if (leader) {
+        for (int s = 0; s < kBulkStages; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (WITH_SUM) __syncthreads();
+    const uint64_t pol = l2_evict_first_policy();
+    uint64_t A = 0, B = 0;
+    BulkCursor prod(blockIdx.x), cons(blockIdx.x);
+    BulkChunk pc, cc;
+    uint32_t issued = 0;
+    auto issue = [&](const BulkChunk &c) {        // leader only: chunk number `issued` -> stage issued % S
+        uint64_t *bar = &full[issued % kBulkStages];
+        const uint32_t nb = c.len & ~15u;
+        mbar_arrive_expect_tx(bar, nb);           // nb == 0 (a tensor's < 16-byte tail chunk): the phase completes at once
+        if (nb) bulk_g2s(bulk_smem + (size_t)(issued % kBulkStages) * kBulkChunk, UNPACK ? image + c.ioff : c.tensor, nb, bar, pol);
+        ++issued;
+    };
+    if (leader)
+        for (int i = 0; i < kBulkStages - 2; ++i)
+            if (prod.next(pd, pc)) issue(pc);
+    for (uint32_t q = 0; cons.next(pd, cc); ++q) {
+        if (WITH_SUM) __syncthreads();            // every thread is done with the tiles of chunks < q
+        if (leader && prod.next(pd, pc)) {
+            bulk_wait_read<1>();                  // store(q-2) has drained the stage about to be refilled
+            issue(pc);
+        }
+        const uint32_t stage = q % kBulkStages;
+        uint8_t *tile = bulk_smem + (size_t)stage * kBulkChunk;
+        const uint32_t nb = cc.len & ~15u;
+        mbar_wait(&full[stage], (q / kBulkStages) & 1u);
+        if (leader) {
+            if (nb) bulk_s2g(UNPACK ? cc.tensor : image + cc.ioff, tile, nb, pol);
+            bulk_commit();                        // one group per chunk, empty or not: keeps wait_group counts uniform
+        }
+        const uint64_t w0 = cc.ioff / 4;
+        if (WITH_SUM) {
+            const uint4 *tv = reinterpret_cast<const uint4 *>(tile);
+            const uint32_t nvec = nb / 16;
+#pragma unroll 4
+            for (uint32_t k = threadIdx.x; k < nvec; k += kBulkThreads) sum_vec(tv[k], w0 + 4ull * k, A, B);
+        }
+        const int rem = (int)(cc.len & 15u);
+        if (rem && leader) {                      // zero-padded last vector of the tensor, as in pack_kernel
+            uint4 w;
+            uint8_t *img = image + cc.ioff + nb;
+            if (UNPACK) {
+                w = ld_stream(img);
+                store_bytes(cc.tensor + nb, w, rem);
+            } else {
+                w = load_bytes(cc.tensor + nb, rem);
+                st_stream(img, w);
+            }
+            if (WITH_SUM) sum_vec(w, w0 + nb / 4, A, B);
+        }
+    }
+    if (leader) bulk_wait_all();                  // shared memory must outlive the stores reading it
+    if (WITH_SUM) block_sum_commit(A, B, sum);
+}
+
 // Resident CTAs per SM, measured on B200 over 2 GiB tensors (round 1): the copy-shaped pack / unpack
 // kernels peak with FEW concurrent streams (3 CTAs/SM: 6300 GB/s = 0.98 of the measured copy peak;
 // 8: 0.93), the read-only checksum with many (12: 6855 GB/s; 3: 5401).  PR_CKPT_BLOCKS_PER_SM
@@ -205,6 +377,33 @@ int ckpt_blocks_per_sm(bool copy_shaped) {
 
 }  // namespace
 
+// Validation shared by pr_pack_plan_create and pr_ckpt_pack_noalloc: every slot inside the image (no
+// uint64 wrap-around) and no two non-empty slots overlapping.  `order` is caller-provided scratch of n
+// ints (the no-allocation entry point must not touch the heap).  Empty tensors own no bytes and are
+// left out of the sweep, so one cannot hide an overlap between its neighbours.
+static int validate_slots(const char *who, const void *const *tensor, const uint64_t *nbytes, const uint64_t *dst_off,
+                          int n, uint64_t image_bytes, int *order) {
+    int m = 0;
+    for (int i = 0; i < n; ++i) {
+        PR_REQUIRE(dst_off[i] % 16 == 0, "%s: dst_off[%d]=%llu is not a multiple of 16", who, i,
+                   (unsigned long long)dst_off[i]);
+        PR_REQUIRE(nbytes[i] <= UINT64_MAX - 15, "%s: tensor %d has an impossible size", who, i);
+        const uint64_t padded = (nbytes[i] + 15) / 16 * 16;
+        PR_REQUIRE(dst_off[i] <= image_bytes && padded <= image_bytes - dst_off[i],
+                   "%s: tensor %d (%llu B at %llu) overruns the image (%llu B)", who, i,
+                   (unsigned long long)nbytes[i], (unsigned long long)dst_off[i], (unsigned long long)image_bytes);
+        PR_REQUIRE(nbytes[i] == 0 || tensor[i] != nullptr, "%s: tensor %d is NULL", who, i);
+        if (nbytes[i]) order[m++] = i;
+    }
+    std::sort(order, order + m, [&](int a, int b) { return dst_off[a] < dst_off[b]; });
+    for (int k = 1; k < m; ++k) {
+        const int a = order[k - 1], b = order[k];
+        PR_REQUIRE(dst_off[a] + (nbytes[a] + 15) / 16 * 16 <= dst_off[b], "%s: tensors %d and %d overlap in the image",
+                   who, a, b);
+    }
+    return PR_OK;
+}
+
 struct pr_pack_plan {
     int device = -1;
     int n = 0;
@@ -212,6 +411,7 @@ struct pr_pack_plan {
     uint64_t payload_bytes = 0;
     void *table = nullptr;   // one device allocation holding all five arrays
     PlanDev dev{};
+    bool bulk_ok = true;     // every tensor base is 16-byte aligned: the bulk-copy kernels apply
 };
 
 extern "C" int pr_checksum(const void *data, uint64_t nbytes, uint64_t word_base, uint64_t *sum,
@@ -242,16 +442,12 @@ extern "C" int pr_pack_plan_create(const void *const *tensor, const uint64_t *nb
     PR_REQUIRE(n >= 0 && (n == 0 || (tensor && nbytes && dst_off)), "pr_pack_plan_create: bad table");
     std::vector<uint64_t> ptrs(n), offs(n), lens(n), first(n);
     std::vector<uint32_t> tile_seg;
+    std::vector<int> order(n);
+    int vrc = validate_slots("pr_pack_plan_create", tensor, nbytes, dst_off, n, image_bytes, order.data());
+    if (vrc) return vrc;
     uint64_t payload = 0;
+    bool bulk_ok = true;
     for (int i = 0; i < n; ++i) {
-        PR_REQUIRE(dst_off[i] % 16 == 0, "pr_pack_plan_create: dst_off[%d]=%llu is not a multiple of 16",
-                   i, (unsigned long long)dst_off[i]);
-        uint64_t padded = (nbytes[i] + 15) / 16 * 16;
-        PR_REQUIRE(dst_off[i] + padded <= image_bytes,
-                   "pr_pack_plan_create: tensor %d (%llu B at %llu) overruns the image (%llu B)", i,
-                   (unsigned long long)nbytes[i], (unsigned long long)dst_off[i],
-                   (unsigned long long)image_bytes);
-        PR_REQUIRE(nbytes[i] == 0 || tensor[i] != nullptr, "pr_pack_plan_create: tensor %d is NULL", i);
         ptrs[i] = (uint64_t)(uintptr_t)tensor[i];
         offs[i] = dst_off[i];
         lens[i] = nbytes[i];
@@ -259,23 +455,16 @@ extern "C" int pr_pack_plan_create(const void *const *tensor, const uint64_t *nb
         uint64_t nt = (nbytes[i] + kTileBytes - 1) / kTileBytes;
         tile_seg.insert(tile_seg.end(), nt, (uint32_t)i);
         payload += nbytes[i];
+        if (nbytes[i] && !pr_aligned16(tensor[i])) bulk_ok = false;
     }
-    // reject overlapping slots (sorted sweep)
-    {
-        std::vector<int> order(n);
-        for (int i = 0; i < n; ++i) order[i] = i;
-        std::sort(order.begin(), order.end(), [&](int a, int b) { return offs[a] < offs[b]; });
-        for (int k = 1; k < n; ++k) {
-            int a = order[k - 1], b = order[k];
-            PR_REQUIRE(offs[a] + (lens[a] + 15) / 16 * 16 <= offs[b] || lens[a] == 0 || lens[b] == 0,
-                       "pr_pack_plan_create: tensors %d and %d overlap in the image", a, b);
-        }
-    }
+    int device = 0;
+    PR_CUDA(cudaGetDevice(&device));
     auto *plan = new pr_pack_plan();
+    plan->device = device;
     plan->n = n;
     plan->image_bytes = image_bytes;
     plan->payload_bytes = payload;
-    PR_CUDA(cudaGetDevice(&plan->device));
+    plan->bulk_ok = bulk_ok;
     const uint64_t ntiles = tile_seg.size();
     const size_t seg_bytes = sizeof(uint64_t) * (size_t)n;
     const size_t total = 4 * seg_bytes + sizeof(uint32_t) * ntiles;
@@ -318,14 +507,67 @@ extern "C" int pr_pack_plan_destroy(pr_pack_plan *plan) {
     return PR_OK;
 }
 
+// Default grid of the bulk-copy kernels.  One CTA keeps kBulkStages - 2 chunks of loads in flight, so a few
+// dozen CTAs already move data at a large fraction of the HBM rate while leaving most SMs to whatever runs
+// beside the snapshot (the next forward pass).  PR_CKPT_BULK_BLOCKS overrides; per call: max_blocks.
+constexpr int kBulkDefaultBlocks = 64;
+
+static int bulk_default_blocks() {
+    static int env = [] {
+        const char *e = getenv("PR_CKPT_BULK_BLOCKS");
+        int b = e ? atoi(e) : 0;
+        return b > 0 ? b : 0;
+    }();
+    return env ? env : kBulkDefaultBlocks;
+}
+
+template <bool UNPACK, bool WITH_SUM>
+static int launch_bulk(const PlanDev &pd, uint8_t *image, uint64_t *sum, int grid, cudaStream_t stream) {
+    auto kernel = pack_bulk_kernel<UNPACK, WITH_SUM>;
+    static bool configured[64] = {};
+    int dev = 0;
+    PR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+        PR_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBulkSmemBytes));
+        if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+    kernel<<<grid, kBulkThreads, kBulkSmemBytes, stream>>>(pd, image, sum);
+    PR_CUDA(cudaGetLastError());
+    pr_count_launch();
+    return PR_OK;
+}
+
 template <bool UNPACK>
-static int launch_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, void *stream_) {
-    PR_REQUIRE(plan != nullptr, "pr_ckpt_%s: plan is NULL", UNPACK ? "unpack" : "pack");
+static int launch_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, int algo, int max_blocks, void *stream_) {
+    const char *who = UNPACK ? "pr_ckpt_unpack" : "pr_ckpt_pack";
+    PR_REQUIRE(plan != nullptr, "%s: plan is NULL", who);
+    PR_REQUIRE(algo == PR_PACK_AUTO || algo == PR_PACK_LDG || algo == PR_PACK_BULK, "%s: algo %d unknown", who, algo);
+    PR_REQUIRE(max_blocks >= 0, "%s: max_blocks must be >= 0", who);
     if (plan->dev.ntiles == 0) return PR_OK;
-    PR_REQUIRE(image != nullptr && pr_aligned16(image), "pr_ckpt_%s: image must be non-NULL and 16-B aligned",
-               UNPACK ? "unpack" : "pack");
+    PR_REQUIRE(image != nullptr && pr_aligned16(image), "%s: image must be non-NULL and 16-B aligned", who);
     cudaStream_t stream = (cudaStream_t)stream_;
+    bool bulk = algo == PR_PACK_BULK;
+    if (algo != PR_PACK_LDG) {
+        // bulk copies address device memory; an image in mapped pinned host memory takes the LDG/STG kernel
+        cudaPointerAttributes attr;
+        const bool on_device = cudaPointerGetAttributes(&attr, image) == cudaSuccess && attr.type == cudaMemoryTypeDevice;
+        cudaGetLastError();
+        if (algo == PR_PACK_BULK) {
+            PR_REQUIRE(plan->bulk_ok, "%s: PR_PACK_BULK needs every tensor base 16-byte aligned", who);
+            PR_REQUIRE(on_device, "%s: PR_PACK_BULK needs the image in device memory", who);
+        } else {
+            bulk = plan->bulk_ok && on_device;
+        }
+    }
+    if (bulk) {
+        uint64_t cap = (uint64_t)(max_blocks > 0 ? max_blocks : bulk_default_blocks());
+        if (cap > (uint64_t)pr_sm_count()) cap = (uint64_t)pr_sm_count();     // 192 KiB of shared memory: one CTA per SM
+        int grid = (int)(plan->dev.ntiles < cap ? plan->dev.ntiles : cap);
+        return sum ? launch_bulk<UNPACK, true>(plan->dev, (uint8_t *)image, sum, grid, stream)
+                   : launch_bulk<UNPACK, false>(plan->dev, (uint8_t *)image, nullptr, grid, stream);
+    }
     uint64_t cap = (uint64_t)pr_sm_count() * ckpt_blocks_per_sm(true);
+    if (max_blocks > 0 && (uint64_t)max_blocks < cap) cap = (uint64_t)max_blocks;
     int grid = (int)(plan->dev.ntiles < cap ? plan->dev.ntiles : cap);
     if (sum)
         pack_kernel<UNPACK, true><<<grid, kThreads, 0, stream>>>(plan->dev, (uint8_t *)image, sum);
@@ -337,11 +579,21 @@ static int launch_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, voi
 }
 
 extern "C" int pr_ckpt_pack(const pr_pack_plan *plan, void *image, uint64_t *sum, void *stream) {
-    return launch_pack<false>(plan, image, sum, stream);
+    return launch_pack<false>(plan, image, sum, PR_PACK_AUTO, 0, stream);
 }
 
 extern "C" int pr_ckpt_unpack(const pr_pack_plan *plan, const void *image, uint64_t *sum, void *stream) {
-    return launch_pack<true>(plan, const_cast<void *>(image), sum, stream);
+    return launch_pack<true>(plan, const_cast<void *>(image), sum, PR_PACK_AUTO, 0, stream);
+}
+
+extern "C" int pr_ckpt_pack_ex(const pr_pack_plan *plan, void *image, uint64_t *sum, int algo, int max_blocks,
+                               void *stream) {
+    return launch_pack<false>(plan, image, sum, algo, max_blocks, stream);
+}
+
+extern "C" int pr_ckpt_unpack_ex(const pr_pack_plan *plan, const void *image, uint64_t *sum, int algo, int max_blocks,
+                                 void *stream) {
+    return launch_pack<true>(plan, const_cast<void *>(image), sum, algo, max_blocks, stream);
 }
 
 // ---- host arena + copies + file writer --------------------------------------------------
@@ -476,17 +728,12 @@ extern "C" int pr_ckpt_pack_noalloc(const void *const *tensor, const uint64_t *n
     uint64_t *lens = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 2 * kNoAllocSegBytes);
     uint64_t *first = reinterpret_cast<uint64_t *>(g_noalloc_host_table + 3 * kNoAllocSegBytes);
     uint32_t *tile_seg = reinterpret_cast<uint32_t *>(g_noalloc_host_table + 4 * kNoAllocSegBytes);
+    int vrc = validate_slots("pr_ckpt_pack_noalloc", tensor, nbytes, dst_off, n, image_bytes, g_noalloc_order);
+    if (vrc) return vrc;
     uint64_t ntiles = 0;
     for (int i = 0; i < n; ++i) {
-        PR_REQUIRE(dst_off[i] % 16 == 0, "pr_ckpt_pack_noalloc: dst_off[%d]=%llu is not a multiple of 16", i,
-                   (unsigned long long)dst_off[i]);
-        uint64_t padded = (nbytes[i] + 15) / 16 * 16;
-        PR_REQUIRE(dst_off[i] + padded <= image_bytes,
-                   "pr_ckpt_pack_noalloc: tensor %d (%llu B at %llu) overruns the image (%llu B)", i,
-                   (unsigned long long)nbytes[i], (unsigned long long)dst_off[i], (unsigned long long)image_bytes);
-        PR_REQUIRE(nbytes[i] == 0 || tensor[i] != nullptr, "pr_ckpt_pack_noalloc: tensor %d is NULL", i);
         uint64_t nt = (nbytes[i] + kTileBytes - 1) / kTileBytes;
-        PR_REQUIRE(ntiles + nt <= kNoAllocMaxTiles,
+        PR_REQUIRE(nt <= kNoAllocMaxTiles && ntiles + nt <= kNoAllocMaxTiles,
                    "pr_ckpt_pack_noalloc: the tensors need more than %llu tiles of %llu KiB (about %llu GiB of payload); "
                    "use pr_pack_plan_create for larger images",
                    (unsigned long long)kNoAllocMaxTiles, (unsigned long long)(kTileBytes >> 10),
@@ -497,21 +744,17 @@ extern "C" int pr_ckpt_pack_noalloc(const void *const *tensor, const uint64_t *n
         first[i] = ntiles;
         for (uint64_t t = 0; t < nt; ++t) tile_seg[ntiles + t] = (uint32_t)i;
         ntiles += nt;
-        g_noalloc_order[i] = i;
-    }
-    std::sort(g_noalloc_order, g_noalloc_order + n, [&](int a, int b) { return offs[a] < offs[b]; });
-    for (int k = 1; k < n; ++k) {
-        int a = g_noalloc_order[k - 1], b = g_noalloc_order[k];
-        PR_REQUIRE(offs[a] + (lens[a] + 15) / 16 * 16 <= offs[b] || lens[a] == 0 || lens[b] == 0,
-                   "pr_ckpt_pack_noalloc: tensors %d and %d overlap in the image", a, b);
     }
     if (ntiles == 0) return PR_OK;
 
-    // Set-up, once per device: resolve the device address of the array with this device current.
+    // Set-up: resolve the device address of the array with this device current.  The first resolution on
+    // a device is what loads the module and materialises the array there (CUDA loads modules lazily); the
+    // address is remembered per device, and looked up again on every call so that a pointer from before a
+    // cudaDeviceReset is never handed to the kernel (after the first time this is a table lookup).
     int dev = 0;
     PR_CUDA(cudaGetDevice(&dev));
     PR_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "pr_ckpt_pack_noalloc: device ordinal %d unsupported", dev);
-    if (g_noalloc_dev_ptr[dev] == nullptr) {
+    {
         void *ptr = nullptr;
         PR_CUDA(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
         PR_REQUIRE(ptr != nullptr, "pr_ckpt_pack_noalloc: cudaGetSymbolAddress returned NULL");

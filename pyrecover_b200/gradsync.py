@@ -8,16 +8,19 @@ allreduce its Reducer fires inside `loss.backward()` (train.py:269):
     torch/nn/parallel/distributed.py:879-889) -- over torch.distributed (NCCL/gloo =
     bootstrap only), as is the exchange of the CUDA-IPC handles of the symmetric arenas;
   * gradients land in the flat g arena, which IS the NVLink communication buffer (no separate
-    bucket copy as with DDP's gradient_as_bucket_view=False): from a post-accumulate-grad hook per
-    parameter when the exchange overlaps backward, else by one multi-tensor copy in
-    optimizer.step() (no Python runs during backward); the autograd allocations are freed;
+    bucket copy as with DDP's gradient_as_bucket_view=False), by the library's own gather kernel
+    (pr_gather_grads: one launch per bucket, reading every gradient where autograd left it) -- per
+    bucket on the communication stream when the exchange overlaps backward, else once in
+    optimizer.step().  The per-parameter hooks of the overlapping modes only count down (about a
+    microsecond each); the autograd allocations are released after the update and come back from
+    the caching allocator at the same addresses next step (no cudaMalloc in steady state);
   * mode "replicated": buckets of the arena are all-reduced by K1 on a side stream as soon as
     all their gradients have landed (in bucket order, like the Reducer), overlapping the rest
     of backward; optimizer.step() then runs K2 over the whole arena on every rank;
   * mode "fused": optimizer.step() runs ONE kernel: reduce-scatter -> AdamW on the rank's
     slice -> all-gather of the updated parameters (moments are sharded across ranks);
-  * mode "overlap": the same fused kernel, but per bucket and launched from the hooks on a side
-    stream WHILE backward is still running: by the time a bucket's last gradient has landed, the
+  * mode "overlap": gather + the same fused kernel, per bucket, launched on a side stream from the
+    hook of the bucket's last gradient WHILE backward is still running: by the time a bucket's last gradient has landed, the
     autograd nodes that read those parameters have already produced their input gradients
     (weight and input gradients come out of the same node), and a peer can only push new
     parameter values into this rank's arena after this rank's own kernel for that bucket has
@@ -30,9 +33,12 @@ Reducer does (reducer.hpp:500) -- strictly more accurate, bounded in tests/.
 """
 from __future__ import annotations
 
+import os
+import time
 from typing import List, Optional
 
 import torch
+from torch.cuda import nvtx
 
 from . import _lib
 from . import kernels as K
@@ -52,6 +58,16 @@ def slice_of(lo: int, hi: int, esize: int, rank: int, world: int):
     return a, b
 
 
+class _Bucket:
+    """A contiguous run of arena slots [seg_lo, seg_hi) = elements [lo, hi) exchanged by one launch."""
+    __slots__ = ("lo", "hi", "seg_lo", "seg_hi", "members", "pending")
+
+    def __init__(self, lo, hi, seg_lo, seg_hi):
+        self.lo, self.hi, self.seg_lo, self.seg_hi = lo, hi, seg_lo, seg_hi
+        self.members = seg_hi - seg_lo
+        self.pending = self.members
+
+
 class GradSync:
     def __init__(self, process_group=None, mode: str = "replicated", bucket_bytes: int = 256 << 20,
                  overlap: bool = True, max_blocks: int = 0, overlap_blocks: int = 32,
@@ -68,20 +84,24 @@ class GradSync:
                 raise RuntimeError("GradSync needs an initialised torch.distributed process group (bootstrap)")
             self.rank, self.world = dist.get_rank(process_group), dist.get_world_size(process_group)
             self.comm = K.Comm(self.rank, self.world)
-        self.bucket_bytes = int(bucket_bytes)
+        self.bucket_bytes = int(os.environ.get("PYRECOVER_B200_BUCKET_BYTES", bucket_bytes))
         self.overlap = (overlap and mode == "replicated") or mode == "overlap"
-        self.max_blocks = max_blocks
-        # CTAs of a bucket allreduce that runs UNDER backward: NVLink saturates with a few dozen
+        # grid of the fused launch after backward (0 = the kernel's default, one CTA per SM)
+        self.max_blocks = int(os.environ.get("PYRECOVER_B200_FUSED_BLOCKS", max_blocks))
+        # CTAs of a bucket launch that runs UNDER backward: NVLink saturates with a few dozen
         # CTAs, and every CTA taken is an SM the backward GEMMs cannot use
-        self.overlap_blocks = overlap_blocks
+        self.overlap_blocks = int(os.environ.get("PYRECOVER_B200_OVERLAP_BLOCKS", overlap_blocks))
         self.arena: Optional[FlatArena] = None
         self.device = torch.device("cuda", torch.cuda.current_device())
         self.comm_stream = torch.cuda.Stream(device=self.device)
         self._hooks = []
-        self._buckets: List[dict] = []
+        self._buckets: List[_Bucket] = []
         self._next_bucket = 0
-        self._seen = 0
+        self._plan: Optional[K.AdamWPlan] = None
+        self._ev_pool: List[torch.cuda.Event] = []
         self._moments_replicated = True
+        self._n = 0                   # exchanges completed (one per optimizer step)
+        self._seq_after = [0] * 16    # communicator launch sequence number after exchange n, ring
         self._hyper = None            # callable -> dict(lr, beta1, beta2, eps, weight_decay, step) of the NEXT update
 
     def bind_hyperparams(self, fn, optimizer=None) -> None:
@@ -110,45 +130,57 @@ class GradSync:
         # produces gradients in reverse parameter order
         esize = arena.layout.esize
         slots = arena.layout.slots
-        cur_hi = arena.numel
-        members: List[int] = []
+        cur_hi, seg_hi = arena.numel, len(slots)
         for s in reversed(slots):
-            members.append(s.index)
             if (cur_hi - s.offset) * esize >= self.bucket_bytes or s.index == 0:
-                self._buckets.append({"lo": s.offset if s.index else 0, "hi": cur_hi,
-                                      "members": members, "pending": len(members)})
-                cur_hi = s.offset
-                members = []
-        self._bucket_of = {}
-        for bi, b in enumerate(self._buckets):
-            for idx in b["members"]:
-                self._bucket_of[idx] = bi
+                self._buckets.append(_Bucket(s.offset if s.index else 0, cur_hi, s.index, seg_hi))
+                cur_hi, seg_hi = s.offset, s.index
+        if arena.dtype == torch.bfloat16:
+            self._plan = K.AdamWPlan([s.offset for s in slots], [s.numel for s in slots], arena.numel)
         if self.overlap:
-            for q, gv, slot in zip(arena.params, arena.g_views, slots):
-                self._hooks.append(q.register_post_accumulate_grad_hook(self._make_hook(slot.index, gv)))
-        # without overlap nothing has to happen DURING backward: optimizer.step() gathers all
-        # gradients into the arena with one multi-tensor copy (147 python hook calls per step cost
-        # ~4 ms of host time, which a launch-bound loop cannot hide)
+            # one closure per bucket, shared by its parameters: a hook call only counts down; the call
+            # that brings a bucket to zero enqueues its gather + exchange on the communication stream
+            for b in self._buckets:
+                hook = self._make_hook(b)
+                for q in arena.params[b.seg_lo:b.seg_hi]:
+                    self._hooks.append(q.register_post_accumulate_grad_hook(hook))
+        # without overlap nothing happens DURING backward: optimizer.step() gathers all gradients
+        # into the arena with one launch
 
-    def _make_hook(self, index: int, gview: torch.Tensor):
-        def hook(param: torch.nn.Parameter):
-            gview.copy_(param.grad)
-            param.grad = None
-            self._seen += 1
-            b = self._buckets[self._bucket_of[index]]
-            b["pending"] -= 1
-            if self.overlap and self.world > 1:
+    def _make_hook(self, bucket: _Bucket):
+        def hook(_param):
+            bucket.pending -= 1
+            if bucket.pending == 0 and self.world > 1:
                 self._launch_ready_buckets()
         return hook
 
+    def _event(self) -> torch.cuda.Event:
+        return self._ev_pool.pop() if self._ev_pool else torch.cuda.Event()
+
+    def _gather(self, seg_lo: int, seg_hi: int, stream) -> None:
+        """Gradients of tensors [seg_lo, seg_hi) -> their slots of the g arena, on `stream`."""
+        arena = self.arena
+        grads = [q.grad for q in arena.params[seg_lo:seg_hi]]
+        if self._plan is not None:
+            self._plan.gather([None] * seg_lo + grads, arena.g, seg_lo, seg_hi, stream=stream)
+        else:                                      # fp32 arenas (not the reference configuration): library copy
+            with torch.cuda.stream(stream):
+                torch._foreach_copy_(arena.g_views[seg_lo:seg_hi], grads)
+
     def _launch_ready_buckets(self) -> None:
         # strictly in bucket order so every rank issues the same collectives in the same order
-        while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket]["pending"] == 0:
+        while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket].pending == 0:
             b = self._buckets[self._next_bucket]
-            ev = torch.cuda.Event()
+            ev = self._event()
             ev.record(torch.cuda.current_stream())
             self.comm_stream.wait_event(ev)
+            self._ev_pool.append(ev)
             esize = self.arena.layout.esize
+            torch.cuda.nvtx.range_push("grad_sync")
+            # the gradients stay attached to their parameters until optimizer.step() has made the
+            # training stream wait for this stream, so the allocator cannot hand their memory out
+            # while the gather below is still reading it
+            self._gather(b.seg_lo, b.seg_hi, self.comm_stream)
             if self.mode == "overlap":
                 fence = getattr(getattr(self, "_optimizer", None), "_snapshot_fence", None)
                 if fence is not None:      # a checkpoint snapshot may still be reading p / m / v
@@ -156,34 +188,44 @@ class GradSync:
                 h = self._hyper()
                 args = K.adamw_args(h["lr"], h["beta1"], h["beta2"], h["eps"], h["weight_decay"], h["step"],
                                     grad_scale=1.0 / self.world)
-                self.comm.allreduce_adamw(REGION_G, REGION_P, REGION_M, REGION_V, b["lo"], b["hi"] - b["lo"], args,
+                self.comm.allreduce_adamw(REGION_G, REGION_P, REGION_M, REGION_V, b.lo, b.hi - b.lo, args,
                                           max_blocks=self.overlap_blocks, stream=self.comm_stream)
                 self._moments_replicated = False
             else:
-                self.comm.allreduce(REGION_G, b["lo"] * esize, (b["hi"] - b["lo"]) * esize, self.arena.dtype,
+                self.comm.allreduce(REGION_G, b.lo * esize, (b.hi - b.lo) * esize, self.arena.dtype,
                                     1.0 / self.world, max_blocks=self.overlap_blocks, stream=self.comm_stream)
+            torch.cuda.nvtx.range_pop()
             self._next_bucket += 1
 
     # ---- called by B200AdamW.step() ---------------------------------------------------------
     def grads_ready(self) -> bool:
-        if not self.overlap:
-            grads = [q.grad for q in self.arena.params]
-            have = sum(g is not None for g in grads)
+        n = len(self.arena.params)
+        if not self.overlap or self.world == 1:
+            have = sum(q.grad is not None for q in self.arena.params)
             if have == 0:
                 return False
-            if have != len(grads):
-                raise RuntimeError(f"GradSync: {have} of {len(grads)} gradients arrived "
+            if have != n:
+                raise RuntimeError(f"GradSync: {have} of {n} gradients arrived "
                                    "(reference semantics: find_unused_parameters=False)")
-            torch._foreach_copy_(self.arena.g_views, grads)
-            for q in self.arena.params:
-                q.grad = None
+            self._gather(0, n, torch.cuda.current_stream())
+            self._release_grads()          # same stream as the gather: the memory may be reused at once
             return True
-        if self._seen == 0:
+        seen = n - sum(b.pending for b in self._buckets)
+        if seen == 0:
             return False
-        if self._seen != len(self.arena.params):
-            raise RuntimeError(f"GradSync: {self._seen} of {len(self.arena.params)} gradients arrived "
+        if seen != n:
+            raise RuntimeError(f"GradSync: {seen} of {n} gradients arrived "
                                "(reference semantics: find_unused_parameters=False)")
         return True
+
+    def _release_grads(self) -> None:
+        for q in self.arena.params:
+            q.grad = None
+
+    def _rearm(self) -> None:
+        self._next_bucket = 0
+        for b in self._buckets:
+            b.pending = b.members
 
     def reduce_and_step(self, *, lr, beta1, beta2, eps, weight_decay, step, numerics, max_grad_norm=None,
                         norm=None) -> None:
@@ -202,9 +244,11 @@ class GradSync:
             if events is not None:
                 e0.record(cur)
             self._launch_ready_buckets()          # normally a no-op: every bucket was launched by the hooks
-            ev = torch.cuda.Event()
+            ev = self._event()
             ev.record(self.comm_stream)
             cur.wait_event(ev)
+            self._ev_pool.append(ev)
+            self._release_grads()                 # the training stream is now ordered after the gathers
             if events is not None:
                 e1.record(cur)
                 events.append((e0, e1))
@@ -214,8 +258,12 @@ class GradSync:
             args = K.adamw_args(lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0 / self.world)
             if events is not None:
                 e0.record(cur)
+            nvtx.range_push("grad_sync")
+            nvtx.range_push("adamw")             # one launch does both
             self.comm.allreduce_adamw(REGION_G, REGION_P, REGION_M, REGION_V, 0, arena.numel, args,
                                       max_blocks=self.max_blocks, stream=cur)
+            nvtx.range_pop()
+            nvtx.range_pop()
             if events is not None:
                 e1.record(cur)
                 events.append((e0, e1))
@@ -224,14 +272,19 @@ class GradSync:
             if self.world > 1:
                 if self.overlap:
                     self._launch_ready_buckets()
-                    ev = torch.cuda.Event()
+                    ev = self._event()
                     ev.record(self.comm_stream)
                     cur.wait_event(ev)
+                    self._ev_pool.append(ev)
+                    self._release_grads()
                 else:
+                    nvtx.range_push("grad_sync")
                     self.comm.allreduce(REGION_G, 0, arena.layout.nbytes, arena.dtype, 1.0 / self.world,
                                         max_blocks=self.max_blocks, stream=cur)
+                    nvtx.range_pop()
             if events is not None:
                 e0.record(cur)
+            nvtx.range_push("adamw")
             coef = None
             if max_grad_norm:
                 # after the exchange every rank holds the same mean gradient, bit for bit: each computes
@@ -240,14 +293,12 @@ class GradSync:
                 coef = norm.coef
             K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=eps,
                      weight_decay=weight_decay, step=step, numerics=numerics, grad_scale_dev=coef)
+            nvtx.range_pop()
             if events is not None:
                 e1.record(cur)
                 events.append((e0, e1))
-        # re-arm for the next backward
-        self._seen = 0
-        self._next_bucket = 0
-        for b in self._buckets:
-            b["pending"] = len(b["members"])
+        self._rearm()                             # for the next backward
+        self._note_exchange()
         if self.comm.timed_out():
             raise RuntimeError("GradSync: a peer did not reach the gradient exchange (barrier timed out)")
 
@@ -278,12 +329,45 @@ class GradSync:
             e1.record(cur)
             events.append((e0, e1))
         self._moments_replicated = False
-        self._seen = 0
-        self._next_bucket = 0
-        for b in self._buckets:
-            b["pending"] = len(b["members"])
+        self._rearm()
+        self._note_exchange()
         if self.comm.timed_out():
             raise RuntimeError("GradSync: a peer did not reach the gradient exchange (barrier timed out)")
+
+    # ---- stop signal: rank 0's decision reaches every rank inside the exchange itself --------------
+    # The reference broadcasts `should_stop` and reads it back with .item() after EVERY step
+    # (train.py:342-346): one more NCCL launch and a full host<->device synchronisation per step.  Here
+    # rank 0 drops the number of the exchange after which everybody stops into its signal word; the begin
+    # barrier of every K1 launch forwards that word to each rank's host (pr_comm_signal_*), and the host
+    # looks at it without synchronising anything.  The decision takes effect STOP_LAG steps later, on
+    # every rank at the same step: by then each rank has provably seen it (it only waits, if at all, for
+    # an exchange that was enqueued STOP_LAG steps ago).
+    STOP_LAG = 2
+
+    def _note_exchange(self) -> None:
+        self._n += 1
+        self._seq_after[self._n % len(self._seq_after)] = self.comm.seq()
+
+    def request_stop(self) -> int:
+        """Rank 0, before the next step is enqueued: everybody stops after exchange number
+        (completed + 1 + STOP_LAG).  Returns that number.  Other ranks' calls are ignored by the kernels."""
+        at = self._n + 1 + self.STOP_LAG
+        if self.rank == 0:
+            self.comm.signal_post(at, stream=torch.cuda.current_stream())
+        return at
+
+    def stop_due(self) -> bool:
+        """Every rank, after a step: has rank 0 asked to stop at or before this exchange?  No device
+        synchronisation: at most a wait for the exchange enqueued STOP_LAG steps ago to have started."""
+        if self._n <= self.STOP_LAG:
+            return False
+        need = self._seq_after[(self._n - self.STOP_LAG) % len(self._seq_after)]
+        while True:
+            seq, val = self.comm.signal_read()
+            if ((seq - need) & 0xffffffff) < 0x80000000 or self.comm.timed_out():
+                break
+            time.sleep(0)
+        return val != 0 and self._n >= val
 
     # ---- sharded-moment bookkeeping (fused mode) ------------------------------------------------
     def replicate_moments(self) -> None:
@@ -293,7 +377,7 @@ class GradSync:
             esize = self.arena.layout.esize
             # ownership follows the launches: one slice set over the whole arena ("fused") or one
             # per bucket ("overlap")
-            ranges = [(0, self.arena.numel)] if self.mode == "fused" else [(b["lo"], b["hi"]) for b in self._buckets]
+            ranges = [(0, self.arena.numel)] if self.mode == "fused" else [(b.lo, b.hi) for b in self._buckets]
             for lo, hi in ranges:
                 self.comm.allgather_slices(REGION_M, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
                 self.comm.allgather_slices(REGION_V, lo * esize, (hi - lo) * esize, max_blocks=self.max_blocks)
@@ -303,7 +387,7 @@ class GradSync:
         """Element ranges over which slices are cut: the whole arena ("replicated", "fused") or every
         bucket ("overlap": one fused launch, hence one set of W slices, per bucket)."""
         if self.mode == "overlap":
-            return [(b["lo"], b["hi"]) for b in self._buckets]
+            return [(b.lo, b.hi) for b in self._buckets]
         return [(0, self.arena.numel)]
 
     def owned_ranges(self, rank: Optional[int] = None, world: Optional[int] = None):

@@ -124,6 +124,16 @@ class AdamWPlan:
         check(lib().pr_adamw_scattered(self._h, p.data_ptr(), self._ptrs, m.data_ptr(), v.data_ptr(), ctypes.byref(a),
                                        stream_ptr(stream)), "pr_adamw_scattered")
 
+    def gather(self, grads: Sequence[Optional[torch.Tensor]], g_arena: torch.Tensor, seg_lo: int = 0,
+               seg_hi: Optional[int] = None, max_blocks: int = 0, stream=None) -> None:
+        """Copy grads[seg_lo:seg_hi] (where autograd left them) into their slots of the flat gradient arena
+        (pr_gather_grads).  `grads` is indexed by tensor; entries outside the range are not looked at."""
+        seg_hi = self.n if seg_hi is None else seg_hi
+        for i in range(seg_lo, seg_hi):
+            self._ptrs[i] = grads[i].data_ptr()
+        check(lib().pr_gather_grads(self._h, self._ptrs, seg_lo, seg_hi, g_arena.data_ptr(), max_blocks,
+                                    stream_ptr(stream)), "pr_gather_grads")
+
     def close(self) -> None:
         if self._h:
             lib().pr_adamw_plan_destroy(self._h)
@@ -175,13 +185,17 @@ class PackPlan:
         check(lib().pr_pack_plan_create(ptrs, lens, offs, n, self.image_bytes, ctypes.byref(self._h)),
               "pr_pack_plan_create")
 
-    def pack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None) -> None:
-        check(lib().pr_ckpt_pack(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
-                                 stream_ptr(stream)), "pr_ckpt_pack")
+    def pack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None,
+             algo: int = _lib.PR_PACK_AUTO, max_blocks: int = 0) -> None:
+        """algo: PR_PACK_AUTO (bulk-copy kernel when every tensor is 16-B aligned and the image is device
+        memory, else the LDG/STG kernel), PR_PACK_LDG, PR_PACK_BULK; max_blocks bounds the grid (0 = default)."""
+        check(lib().pr_ckpt_pack_ex(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
+                                    algo, max_blocks, stream_ptr(stream)), "pr_ckpt_pack")
 
-    def unpack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None) -> None:
-        check(lib().pr_ckpt_unpack(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
-                                   stream_ptr(stream)), "pr_ckpt_unpack")
+    def unpack(self, image_ptr: int, sum_dev: Optional[torch.Tensor] = None, stream=None,
+               algo: int = _lib.PR_PACK_AUTO, max_blocks: int = 0) -> None:
+        check(lib().pr_ckpt_unpack_ex(self._h, image_ptr, sum_dev.data_ptr() if sum_dev is not None else None,
+                                      algo, max_blocks, stream_ptr(stream)), "pr_ckpt_unpack")
 
     def close(self) -> None:
         if self._h:
@@ -326,6 +340,29 @@ class Comm:
         av, use = c_int(), c_int()
         check(lib().pr_comm_multicast(self._h, policy, ctypes.byref(av), ctypes.byref(use)), "pr_comm_multicast")
         return bool(av.value), bool(use.value)
+
+    def stats(self, reset: bool = False):
+        """(ns CTA 0 waited at begin barriers, launches, ns CTA 0 ran) -- synchronises (pr_comm_stats)."""
+        out = (c_uint64 * 3)()
+        check(lib().pr_comm_stats(self._h, out, 1 if reset else 0), "pr_comm_stats")
+        return int(out[0]), int(out[1]), int(out[2])
+
+    def signal_post(self, value: int, stream=None) -> None:
+        check(lib().pr_comm_signal_post(self._h, int(value) & 0xffffffff, stream_ptr(stream)), "pr_comm_signal_post")
+
+    def signal_read(self):
+        """(launch sequence number, rank 0's word) as last forwarded by a collective's begin barrier; no GPU sync."""
+        seq, val = ctypes.c_uint32(), ctypes.c_uint32()
+        check(lib().pr_comm_signal_read(self._h, ctypes.byref(seq), ctypes.byref(val)), "pr_comm_signal_read")
+        return seq.value, val.value
+
+    def seq(self) -> int:
+        s = ctypes.c_uint32()
+        check(lib().pr_comm_seq(self._h, ctypes.byref(s)), "pr_comm_seq")
+        return s.value
+
+    def test_absent_rank(self, rank: int) -> None:
+        check(lib().pr_comm_test_absent_rank(self._h, rank), "pr_comm_test_absent_rank")
 
     def timed_out(self) -> bool:
         e = c_int()

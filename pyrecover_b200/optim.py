@@ -104,7 +104,25 @@ class B200AdamW(torch.optim.Optimizer):
     def _norm_buffers(self) -> K.GradNorm:
         if self._grad_norm is None:
             self._grad_norm = K.GradNorm(self._arenas[0].device)
+            self._nonfinite_host = torch.zeros(1, dtype=torch.float32).pin_memory()
         return self._grad_norm
+
+    def _note_norm(self) -> None:
+        """After a clipped step has been enqueued: bring the sticky non-finite counter to the host with
+        an asynchronous 4-byte copy, so check_finite() never has to synchronise."""
+        if self._grad_norm is not None:
+            self._nonfinite_host.copy_(self._grad_norm.out[3:4], non_blocking=True)
+
+    def check_finite(self) -> None:
+        """The reference raises as soon as the total gradient norm is not finite (utils.py:87,
+        get_total_norm(error_if_nonfinite=True)).  Here the step is enqueued without waiting for the
+        norm, so the device withholds the update by itself (K2 returns when the coefficient is the -1
+        that pr_grad_norm writes for a non-finite norm: p, m, v and the next checkpoint stay clean) and
+        this check raises at the caller's convenience -- train.py calls it at logging frequency and
+        before every save, i.e. up to a few steps late: the one deviation from the reference."""
+        if self._grad_norm is not None and float(self._nonfinite_host[0]) > 0:
+            raise RuntimeError("The total norm of the gradients is non-finite, so it cannot be clipped "
+                               f"({int(self._nonfinite_host[0])} step(s) so far had their update withheld)")
 
     def _numerics(self, group) -> int:
         if self._numerics_override is not None:
@@ -137,6 +155,8 @@ class B200AdamW(torch.optim.Optimizer):
                     lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"], weight_decay=group["weight_decay"],
                     step=self._steps[gi], numerics=self._numerics(group),
                     max_grad_norm=self.max_grad_norm, norm=self._norm_buffers() if self.max_grad_norm else None)
+                if self.max_grad_norm:
+                    self._note_norm()
                 continue
             have = [q.grad is not None for q in arena.params]
             if not any(have):
@@ -154,6 +174,7 @@ class B200AdamW(torch.optim.Optimizer):
             if events is not None:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
+            torch.cuda.nvtx.range_push("adamw")
             coef = None
             if self.max_grad_norm:
                 if len(self._arenas) != 1:
@@ -175,6 +196,9 @@ class B200AdamW(torch.optim.Optimizer):
                 K.adamw_(arena.p, arena.g, arena.m, arena.v, lr=lr, beta1=beta1, beta2=beta2, eps=group["eps"],
                          weight_decay=group["weight_decay"], step=self._steps[gi], numerics=self._numerics(group),
                          grad_scale_dev=coef)
+            torch.cuda.nvtx.range_pop()
+            if coef is not None:
+                self._note_norm()
             if events is not None:
                 e1.record()
                 events.append((e0, e1))

@@ -42,6 +42,7 @@ ALIGN = 256
 COPY_CHUNK = 64 << 20
 _M64 = (1 << 64) - 1
 SHARD_FORMAT = 1
+PACK_BLOCKS = int(os.environ.get("PYRECOVER_B200_PACK_BLOCKS", "32"))
 
 
 def _round_up(x: int, a: int) -> int:
@@ -92,7 +93,11 @@ class Image:
             self.sum_dev.zero_()
         e_read = torch.cuda.Event()
         if self.staging is not None:
-            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side)
+            # the bulk-copy (TMA-staged) pack kernel on a bounded number of CTAs: it runs beside the next
+            # forward pass and should take few SMs from it (PYRECOVER_B200_PACK_BLOCKS, 0 = kernel default)
+            torch.cuda.nvtx.range_push("ckpt_pack")
+            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side, max_blocks=PACK_BLOCKS)
+            torch.cuda.nvtx.range_pop()
             e_read.record(side)
         else:                                    # direct: copy engines read the live tensors, all at once
             for p in self.pieces:
@@ -124,7 +129,9 @@ class Image:
 
         def issue(span):
             o, n = span
+            torch.cuda.nvtx.range_push("ckpt_d2h")
             K.copy_d2h_async(self.host.ptr + o, self.staging[o:o + n], n, 0, stream=side)
+            torch.cuda.nvtx.range_pop()
             ev = torch.cuda.Event()
             ev.record(side)
             return ev
@@ -174,7 +181,10 @@ class Snapshotter:
         self._writer_error: Optional[BaseException] = None
         self._stub_cache: Dict[Any, PT.TensorStub] = {}
         self._layout: Optional[Dict[str, Any]] = None
+        self._skeleton: Optional[Dict[str, Any]] = None
         self.last_stats: Dict[str, Any] = {}
+        self.durable_s: Optional[float] = None      # save_* call -> file renamed, of the last FINISHED write
+        self._durable_reported = True
         # ---- full image layout: one record per dtype; arenas first (p | m | v), extras after ----
         by_dtype: "OrderedDict[torch.dtype, List[torch.Tensor]]" = OrderedDict()
         for a in self.arenas:
@@ -182,9 +192,16 @@ class Snapshotter:
         self._arena_ranges = [(t.data_ptr(), t.data_ptr() + t.numel() * t.element_size())
                               for a in self.arenas for t in (a.p, a.m, a.v)]
         self.extras: List[torch.Tensor] = []
-        for _, t in self.module.state_dict().items():
-            if t.is_cuda and not self._in_arena(t):
-                t = t if t.is_contiguous() else t.contiguous()
+        for name, t in self.module.state_dict().items():
+            # the image is packed from, and restored into, the LIVE tensors: a private contiguous or
+            # device copy made here would go stale after the first optimizer step
+            if not t.is_cuda:
+                raise RuntimeError(f"pyrecover_b200 snapshot: state_dict entry '{name}' lives on {t.device}; every "
+                                   "entry must be a CUDA tensor (keep host-side state out of state_dict or make "
+                                   "the buffer non-persistent)")
+            if not t.is_contiguous():
+                raise RuntimeError(f"pyrecover_b200 snapshot: state_dict entry '{name}' is not contiguous")
+            if not self._in_arena(t):
                 by_dtype.setdefault(t.dtype, []).append(t)
                 self.extras.append(t)
         self.records: "OrderedDict[str, dict]" = OrderedDict()
@@ -344,26 +361,101 @@ class Snapshotter:
         # optimizer.step() waits for this event (a whole forward+backward later)
         self.optimizer._snapshot_fence = e
 
+    def take_durable_time(self) -> Optional[float]:
+        """Seconds from the save_* call to the renamed file of the most recent write that has FINISHED,
+        once per write (None when nothing new finished).  Never blocks: the time-aware policy feeds on
+        it (reference train.py:334-337 measures the same span around its synchronous save)."""
+        if self._durable_reported or (self._writer is not None and self._writer.is_alive()):
+            return None
+        self._durable_reported = True
+        return self.durable_s
+
+    def _check_exchange(self) -> None:
+        """A gradient exchange whose barrier timed out leaves this rank's parameters untouched but
+        the job broken; nothing may be published as a checkpoint from then on."""
+        gs = getattr(self.optimizer, "_grad_sync", None)
+        if gs is not None and gs.comm.timed_out():
+            raise RuntimeError("refusing to write a checkpoint: the gradient exchange timed out waiting for a peer")
+
+    def skeleton(self) -> Dict[str, Any]:
+        """The part of the saved state that never changes during the job, stubified once: every tensor of
+        model.state_dict() and the exp_avg / exp_avg_sq of every parameter, as views into the image
+        records.  A save then costs the training thread only the handful of python scalars that do
+        change (step counts, lr, scheduler counters, RNG state) -- in a loop that is launch-bound on the
+        host, whatever save_* spends on the training thread is GPU idle time."""
+        if self._skeleton is None:
+            small: Dict[torch.dtype, list] = {}
+            model = self.stubify(self.module.state_dict(), small)
+            opt, index_of, idx = {}, {}, 0
+            for group in self.optimizer.param_groups:
+                for q in group["params"]:
+                    st = self.optimizer.state[q]
+                    opt[idx] = {"exp_avg": self.stubify(st["exp_avg"], small),
+                                "exp_avg_sq": self.stubify(st["exp_avg_sq"], small)}
+                    index_of[id(q)] = idx
+                    idx += 1
+            if small:
+                raise RuntimeError("pyrecover_b200 snapshot: a state tensor lies outside the packed image")
+            self._skeleton = {"model": model, "opt": opt, "index_of": index_of, "n_params": idx}
+        return self._skeleton
+
+    def dynamic_state(self, lr_scheduler, sampler, step, epoch, rng_state) -> Dict[str, Any]:
+        """What changes from save to save, copied on the training thread (a few dozen python objects)."""
+        sk = self.skeleton()
+        groups, gsteps = [], []
+        for gi, group in enumerate(self.optimizer.param_groups):
+            g = {k: v for k, v in group.items() if k != "params"}
+            g["params"] = [sk["index_of"][id(q)] for q in group["params"]]
+            groups.append(g)
+            gsteps.append(float(self.optimizer._steps[gi]))
+        dyn = {"epoch": epoch, "step": step, "param_groups": copy.deepcopy(groups), "group_steps": gsteps,
+               "rng_state": rng_state}
+        if lr_scheduler is not None:
+            dyn["lr_scheduler"] = copy.deepcopy(lr_scheduler.state_dict())
+        if sampler and hasattr(sampler, "set_state"):
+            dyn["sampler_state"] = copy.deepcopy(sampler.state_dict())
+        return dyn
+
+    def _assemble(self, dyn: Dict[str, Any], small: Dict[torch.dtype, list]) -> Dict[str, Any]:
+        """Writer thread: skeleton + dynamic part -> the reference's state dict (same keys, same order as
+        pyrecover/checkpoint.py:60-73; optimizer entry as torch.optim.Optimizer.state_dict() lays it out),
+        tensors as stubs.  Every parameter gets its own step scalar, as torch.optim.AdamW hands them out."""
+        sk = self.skeleton()
+        state: Dict[str, Any] = {"epoch": dyn["epoch"], "step": dyn["step"], "model": sk["model"]}
+        opt_state = {}
+        for gi, g in enumerate(dyn["param_groups"]):
+            steps = torch.full((len(g["params"]),), dyn["group_steps"][gi], dtype=torch.float32)
+            for k, idx in enumerate(g["params"]):
+                opt_state[idx] = {"step": self.stubify(steps[k], small), **sk["opt"][idx]}
+        state["optimizer"] = {"state": {i: opt_state[i] for i in sorted(opt_state)}, "param_groups": dyn["param_groups"]}
+        for key in ("lr_scheduler", "sampler_state", "rng_state"):
+            if key in dyn:
+                state[key] = self.stubify(dyn[key], small)
+        return state
+
     # ------------------------------------------------------------------ vanilla (.pt) -----
-    def save_vanilla(self, path: str, state: Dict[str, Any], verify: bool, max_keep: int,
+    def save_vanilla(self, path: str, dyn: Dict[str, Any], verify: bool, max_keep: int,
                      blocking: bool = False) -> None:
-        """`state` is the reference's dict (epoch, step, model, optimizer, lr_scheduler, ...) with
-        live tensors; python leaves are copied now, tensor bytes are captured by the pack."""
+        """`dyn` = dynamic_state(...): the python-side values of this save; tensor bytes are captured by
+        the pack, and the state dict the file holds is put together in the writer thread."""
         t0 = time.perf_counter()
+        self._check_exchange()
         self.wait()                          # the pinned arena is about to be overwritten
         img = self.full()
         e_read, e_copied = img.stage(self.side)
         self._fence_optimizer(e_read)
-        small: Dict[torch.dtype, list] = {}
-        frozen = self.stubify(state, small)
-        small_bufs = {dt: (torch.cat(parts) if len(parts) > 1 else parts[0]) for dt, (parts, _) in small.items()}
         path = str(path)
         self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
+        self._durable_reported = False
 
         def work():
             t1 = time.perf_counter()
             e_copied.synchronize()
+            self._check_exchange()           # everything up to the pack has run: a timed-out exchange shows by now
             t2 = time.perf_counter()
+            small: Dict[torch.dtype, list] = {}
+            frozen = self._assemble(dyn, small)
+            small_bufs = {dt: (torch.cat(parts) if len(parts) > 1 else parts[0]) for dt, (parts, _) in small.items()}
             records = [(key, (r["nbytes"], img.drain(self.side, r["off"], r["off"] + r["nbytes"])))
                        for key, r in self.records.items()]
             refs = {}
@@ -382,8 +474,10 @@ class Snapshotter:
             with open(path + ".b200sum", "w") as f:
                 json.dump({"sum64": [A, B], "image_bytes": img.image_bytes, "file_bytes": info["bytes"],
                            "record_offsets": info["offsets"]}, f)
+            self.durable_s = time.perf_counter() - t0
             rotate_files(Path(path).parent, max_keep)
-            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=info["bytes"])
+            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=info["bytes"],
+                                   durable_s=self.durable_s)
 
         self._spawn(work)
         if blocking:
@@ -417,10 +511,12 @@ class Snapshotter:
         rank 0 also writes `meta.pt` (python-side state) and rotates old directories.  The
         directory is complete when `COMPLETE_<rank>` exists for every rank."""
         t0 = time.perf_counter()
+        self._check_exchange()
         self.wait()
         img = self.shard(rank, world)
         e_read, e_copied = img.stage(self.side)
         self._fence_optimizer(e_read)
+        self._durable_reported = False
         small_state = _to_cpu(small_state)
         if rank == 0:
             small_state["layout"] = self.tensor_layout()
@@ -431,6 +527,7 @@ class Snapshotter:
             t1 = time.perf_counter()
             d.mkdir(parents=True, exist_ok=True)
             e_copied.synchronize()
+            self._check_exchange()
             t2 = time.perf_counter()
             shard_path = d / f"shard_{rank:05d}.bin"
             PT.write_raw(str(shard_path), img.drain(self.side))
@@ -445,9 +542,11 @@ class Snapshotter:
             else:
                 torch.save({"rng_state": small_state.get("rng_state")}, str(d / f"rng_{rank:05d}.pt"))
             _write_text_atomic(d / f"COMPLETE_{rank:05d}", str(world))
+            self.durable_s = time.perf_counter() - t0
             if rank == 0:
                 rotate_dirs(d.parent, max_keep)
-            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=img.image_bytes)
+            self.last_stats.update(d2h_wait_s=t2 - t1, write_s=time.perf_counter() - t2, file_bytes=img.image_bytes,
+                                   durable_s=self.durable_s)
 
         self._spawn(work)
         if blocking:

@@ -170,12 +170,31 @@ def main():
         cur += (t.numel() * 2 + 255) // 256 * 256
     image = torch.zeros(cur, dtype=torch.uint8, device=dev)
     plan = K.PackPlan(views, offs, cur)
-    ms, best = timeit(lambda: plan.pack(image.data_ptr(), s), a.iters)
-    row("pr_ckpt_pack p+m+v (+sum)", ms, best, 2 * 6 * n)
-    ms, best = timeit(lambda: plan.pack(image.data_ptr(), None), a.iters)
-    row("pr_ckpt_pack p+m+v (no sum)", ms, best, 2 * 6 * n)
-    ms, best = timeit(lambda: plan.unpack(image.data_ptr(), s), a.iters)
-    row("pr_ckpt_unpack p+m+v (+sum)", ms, best, 2 * 6 * n)
+    from pyrecover_b200 import _lib
+    ms, best = timeit(lambda: plan.pack(image.data_ptr(), s, algo=_lib.PR_PACK_LDG), a.iters)
+    row("pr_ckpt_pack LDG/STG p+m+v (+sum)", ms, best, 2 * 6 * n)
+    ms, best = timeit(lambda: plan.pack(image.data_ptr(), None, algo=_lib.PR_PACK_LDG), a.iters)
+    row("pr_ckpt_pack LDG/STG (no sum)", ms, best, 2 * 6 * n)
+    ms, best = timeit(lambda: plan.unpack(image.data_ptr(), s, algo=_lib.PR_PACK_LDG), a.iters)
+    row("pr_ckpt_unpack LDG/STG (+sum)", ms, best, 2 * 6 * n)
+    # bulk-copy (TMA-staged) kernel: grid sweep -- how few CTAs carry the copy
+    for blocks in (8, 16, 24, 32, 48, 64, 96, 148):
+        ms, best = timeit(lambda: plan.pack(image.data_ptr(), s, algo=_lib.PR_PACK_BULK, max_blocks=blocks), a.iters)
+        row(f"pr_ckpt_pack BULK {blocks:3d} CTAs (+sum)", ms, best, 2 * 6 * n)
+    for blocks in (32, 64, 148):
+        ms, best = timeit(lambda: plan.pack(image.data_ptr(), None, algo=_lib.PR_PACK_BULK, max_blocks=blocks), a.iters)
+        row(f"pr_ckpt_pack BULK {blocks:3d} CTAs (no sum)", ms, best, 2 * 6 * n)
+        ms, best = timeit(lambda: plan.unpack(image.data_ptr(), s, algo=_lib.PR_PACK_BULK, max_blocks=blocks), a.iters)
+        row(f"pr_ckpt_unpack BULK {blocks:3d} CTAs (+sum)", ms, best, 2 * 6 * n)
+    # gather: scattered gradients -> flat arena (pr_gather_grads), 4 B per element
+    gchunks = [c.clone() for c in torch.split(g, chunk)]
+    aplan = K.AdamWPlan([i * chunk for i in range(len(gchunks))], [c.numel() for c in gchunks], chunk * len(gchunks))
+    garena = torch.zeros(chunk * len(gchunks), dtype=torch.bfloat16, device=dev)
+    ms, best = timeit(lambda: aplan.gather(gchunks, garena), a.iters)
+    row("pr_gather_grads (2 B r + 2 B w)", ms, best, 4 * n)
+    ms, best = timeit(lambda: torch._foreach_copy_(list(torch.split(garena, chunk)), gchunks), a.iters)
+    row("torch._foreach_copy_ same tensors", ms, best, 4 * n)
+    del gchunks, garena
     # D2H of the image into the pinned arena (PCIe leg)
     arena = K.HostArena(cur)
     ms, best = timeit(lambda: K.copy_d2h_async(arena.ptr, image, cur, 64 << 20), 3, warmup=1)

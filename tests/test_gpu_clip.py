@@ -54,9 +54,24 @@ def test_grad_norm_nonfinite_zero_and_disabled(cuda_lib, oracle):
     assert gn.out[:3].tolist() == [0.0, 1.0, 0.0]             # zero gradient: coefficient clamps to 1
     g[17] = float("inf")
     gn.compute(g, 1.0)
-    norm, coef, bad = gn.out[:3].tolist()
-    assert bad == 1.0 and coef == 1.0 and not np.isfinite(norm)   # the reference raises here (error_if_nonfinite)
+    norm, coef, bad, sticky = gn.out.tolist()
+    # the reference raises here (error_if_nonfinite); the device writes the "withhold the update" coefficient
+    assert bad == 1.0 and coef == -1.0 and not np.isfinite(norm) and sticky == 1.0
     assert oracle.grad_norm(_bits(g.cpu()), 1.0)[2] is True
+    # K2 given that coefficient leaves p, m, v untouched -- flat, scattered, both numerics
+    n = 4096
+    p = (torch.randn(n) * 0.02).bfloat16().cuda()
+    m = (torch.randn(n) * 1e-3).bfloat16().cuda()
+    v = (torch.rand(n) * 1e-6).bfloat16().cuda()
+    p0, m0, v0 = p.clone(), m.clone(), v.clone()
+    for numerics in (0, 1):
+        K.adamw_(p, g, m, v, lr=1e-3, step=2, numerics=numerics, grad_scale_dev=gn.coef)
+        plan = K.AdamWPlan([0, 2048], [2048, 2048], n)
+        plan.step(p, [g[:2048], g[2048:]], m, v, lr=1e-3, step=2, numerics=numerics, grad_scale_dev=gn.coef)
+        torch.cuda.synchronize()
+        assert torch.equal(p, p0) and torch.equal(m, m0) and torch.equal(v, v0)
+    gn.compute(g, 1.0)
+    assert gn.out[3].item() == 2.0                            # sticky count of non-finite norms
     g[17] = 2.0
     gn.compute(g, 0.0)                                        # max_norm <= 0: report the norm, never scale
     assert gn.out[:3].tolist() == [2.0, 1.0, 0.0]

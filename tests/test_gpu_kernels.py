@@ -280,9 +280,14 @@ def _ragged_tensors(seed, sizes, dtype=torch.uint8):
     return [torch.randint(0, 256, (s,), dtype=torch.uint8, generator=g) for s in sizes]
 
 
+@pytest.mark.parametrize("algo", ["auto", "ldg", "bulk"])
 @pytest.mark.parametrize("sizes", [[0, 1, 15, 16, 17, 4096, 70001], [65536, 65536 * 3 + 16, 5], [1 << 22] * 3])
-def test_pack_unpack_vs_oracle(cuda_lib, oracle, sizes):
+def test_pack_unpack_vs_oracle(cuda_lib, oracle, sizes, algo):
+    """Both pack kernels (LDG/STG through registers; bulk copies staged through shared memory) against
+    the oracle, bit for bit: image bytes, PR-SUM64, and the round trip through unpack."""
+    from pyrecover_b200 import _lib
     from pyrecover_b200 import kernels as K
+    code = {"auto": _lib.PR_PACK_AUTO, "ldg": _lib.PR_PACK_LDG, "bulk": _lib.PR_PACK_BULK}[algo]
     host = _ragged_tensors(len(sizes), sizes)
     dev = [h.cuda() for h in host]
     offs, cur = [], 0
@@ -293,7 +298,7 @@ def test_pack_unpack_vs_oracle(cuda_lib, oracle, sizes):
     plan = K.PackPlan(dev, offs, cur)
     image = torch.zeros(cur, dtype=torch.uint8, device="cuda")
     s = torch.zeros(2, dtype=torch.int64, device="cuda")
-    plan.pack(image.data_ptr(), s)
+    plan.pack(image.data_ptr(), s, algo=code)
     ref_image, ref_sum = oracle.pack([h.numpy() for h in host], offs, cur)
     assert np.array_equal(image.cpu().numpy(), ref_image)
     assert K._sum_to_ints(s) == ref_sum
@@ -301,10 +306,60 @@ def test_pack_unpack_vs_oracle(cuda_lib, oracle, sizes):
     fresh = [torch.full_like(d, 0xAB) for d in dev]
     plan2 = K.PackPlan(fresh, offs, cur)
     s2 = torch.zeros(2, dtype=torch.int64, device="cuda")
-    plan2.unpack(image.data_ptr(), s2)
+    plan2.unpack(image.data_ptr(), s2, algo=code)
     for a, b in zip(fresh, host):
         assert torch.equal(a.cpu(), b)
     assert K._sum_to_ints(s2) == ref_sum
+    # without a checksum (the elected thread alone runs the bulk kernel)
+    image2 = torch.zeros(cur, dtype=torch.uint8, device="cuda")
+    plan.pack(image2.data_ptr(), None, algo=code)
+    assert torch.equal(image2, image)
+
+
+@pytest.mark.parametrize("max_blocks", [1, 3, 32, 148])
+def test_pack_bulk_pipeline_depth(cuda_lib, oracle, max_blocks):
+    """The bulk kernel's mbarrier ring wraps many times per CTA (1 CTA: every chunk of 40 MB goes through
+    6 stages), tensors end in partial chunks and in < 16-byte tails; pack == oracle, unpack restores."""
+    from pyrecover_b200 import _lib
+    from pyrecover_b200 import kernels as K
+    sizes = [(5 << 20) + 48, 32768, 32768 + 16, 65536 * 7 + 5, 16, 3, (33 << 20) + 32768 + 7]
+    host = _ragged_tensors(77, sizes)
+    dev = [h.cuda() for h in host]
+    offs, cur = [], 0
+    for s in sizes:
+        offs.append(cur)
+        cur += (s + 255) // 256 * 256
+    plan = K.PackPlan(dev, offs, cur)
+    image = torch.zeros(cur, dtype=torch.uint8, device="cuda")
+    s = torch.zeros(2, dtype=torch.int64, device="cuda")
+    plan.pack(image.data_ptr(), s, algo=_lib.PR_PACK_BULK, max_blocks=max_blocks)
+    ref_image, ref_sum = oracle.pack([h.numpy() for h in host], offs, cur)
+    assert np.array_equal(image.cpu().numpy(), ref_image)
+    assert K._sum_to_ints(s) == ref_sum
+    fresh = [torch.full_like(d, 0x5C) for d in dev]
+    plan2 = K.PackPlan(fresh, offs, cur)
+    s2 = torch.zeros(2, dtype=torch.int64, device="cuda")
+    plan2.unpack(image.data_ptr(), s2, algo=_lib.PR_PACK_BULK, max_blocks=max_blocks)
+    for a, b in zip(fresh, host):
+        assert torch.equal(a.cpu(), b)
+    assert K._sum_to_ints(s2) == ref_sum
+
+
+def test_pack_bulk_rejects_what_it_cannot_do(cuda_lib):
+    from pyrecover_b200 import _lib
+    from pyrecover_b200 import kernels as K
+    base = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    image = torch.zeros(8192, dtype=torch.uint8, device="cuda")
+    plan = K.PackPlan([base[1:1001]], [0], 8192)
+    with pytest.raises(RuntimeError, match="16-byte aligned"):
+        plan.pack(image.data_ptr(), None, algo=_lib.PR_PACK_BULK)
+    plan.pack(image.data_ptr(), None)            # AUTO falls back to the LDG/STG kernel
+    arena = K.HostArena(8192)
+    plan2 = K.PackPlan([base[:1024]], [0], 8192)
+    with pytest.raises(RuntimeError, match="device memory"):
+        plan2.pack(arena.device_ptr(), None, algo=_lib.PR_PACK_BULK)
+    torch.cuda.synchronize()
+    arena.close()
 
 
 def test_pack_unaligned_sources(cuda_lib, oracle):
@@ -363,6 +418,11 @@ def test_pack_plan_rejects_bad_layout(cuda_lib):
         K.PackPlan([a], [0], 64)
     with pytest.raises(RuntimeError, match="overlap"):
         K.PackPlan([a, a], [0, 64], 512)
+    # an empty tensor sorted between two overlapping ones must not hide the overlap
+    z = torch.zeros(0, dtype=torch.uint8, device="cuda")
+    with pytest.raises(RuntimeError, match="overlap"):
+        K.PackPlan([a, z, a], [0, 16, 32], 512)
+    K.PackPlan([a, z, a], [0, 112, 112], 512).close()      # an empty slot may share an offset
 
 
 # --------------------------------------------------------------------------- K1 (emulated)
@@ -463,4 +523,83 @@ def test_allreduce_adamw_fused_emulated(cuda_lib, oracle, world):
     torch.cuda.synchronize()
     for r in range(world):
         assert np.array_equal(_bits(M[r]), mb) and np.array_equal(_bits(V[r]), vb)
+    c.close()
+
+
+def test_gather_grads_vs_copy(cuda_lib):
+    """pr_gather_grads: scattered gradients -> flat arena slots, bit for bit, any tensor sub-range, ragged tails."""
+    from pyrecover_b200 import kernels as K
+    numels = [16384 * 3 + 24, 8, 4096, 16384, 5, 70000]
+    offs, cur = [], 0
+    for n in numels:
+        offs.append(cur)
+        cur += (n + 127) // 128 * 128
+    plan = K.AdamWPlan(offs, numels, cur)
+    gen = torch.Generator().manual_seed(3)
+    grads = [(torch.randn(n, generator=gen)).bfloat16().cuda() for n in numels]
+    for lo, hi, blocks in ((0, len(numels), 0), (2, 5, 0), (0, 1, 2), (5, 6, 1)):
+        arena = torch.full((cur,), 7.0, dtype=torch.bfloat16, device="cuda")
+        want = arena.clone()
+        for i in range(lo, hi):
+            want[offs[i]:offs[i] + numels[i]] = grads[i]
+        plan.gather(grads, arena, lo, hi, max_blocks=blocks)
+        torch.cuda.synchronize()
+        assert torch.equal(arena.view(torch.int16), want.view(torch.int16)), (lo, hi)
+
+
+def test_comm_timeout_leaves_data_untouched(cuda_lib, monkeypatch):
+    """A rank that never reaches the barrier: the others give up after PR_COMM_TIMEOUT_S, raise the error
+    word and return BEFORE reading or writing any gradient, parameter or moment; the communicator then
+    refuses further work."""
+    from pyrecover_b200 import kernels as K
+    monkeypatch.setenv("PR_COMM_TIMEOUT_S", "1")
+    world, nelem = 2, 8 * 4096
+    c = _emu_comm(world, nelem * 2, regions=(0, 1, 2, 3))
+    tens = [[c.region_tensor(k, torch.bfloat16, r) for r in range(world)] for k in range(4)]
+    gen = torch.Generator().manual_seed(1)
+    for k in range(4):
+        for r in range(world):
+            tens[k][r].copy_((torch.randn(nelem, generator=gen) * 1e-2).abs().bfloat16())
+    before = [[t.clone() for t in row] for row in tens]
+    c.test_absent_rank(1)
+    args = K.adamw_args(1e-3, 0.9, 0.999, 1e-8, 0.01, step=1, grad_scale=0.5)
+    c.allreduce_adamw(0, 1, 2, 3, 0, nelem, args)
+    torch.cuda.synchronize()
+    assert c.timed_out()
+    for row, brow in zip(tens, before):
+        for t, b in zip(row, brow):
+            assert torch.equal(t, b)
+    with pytest.raises(RuntimeError, match="timed out"):
+        c.allreduce(0, 0, nelem * 2, torch.bfloat16, 0.5)
+    c.close()
+    # the plain allreduce too
+    c = _emu_comm(world, nelem * 2)
+    bufs = [c.region_tensor(0, torch.bfloat16, r) for r in range(world)]
+    for b in bufs:
+        b.fill_(1.0)
+    c.test_absent_rank(0)
+    c.allreduce(0, 0, nelem * 2, torch.bfloat16, 0.5, algo=2)
+    torch.cuda.synchronize()
+    assert c.timed_out() and all(float(b.min()) == 1.0 and float(b.max()) == 1.0 for b in bufs)
+    c.close()
+
+
+def test_comm_stats_and_signal_word(cuda_lib):
+    """The begin barrier of a collective forwards rank 0's signal word (and the launch's sequence number)
+    to the host without any synchronising call; the device-side clock counts launches and their time."""
+    c = _emu_comm(2, 1 << 20)
+    for r in range(2):
+        c.region_tensor(0, torch.bfloat16, r).fill_(1.0)
+    assert c.signal_read() == (0, 0)
+    c.allreduce(0, 0, 1 << 20, torch.bfloat16, 0.5, algo=2)
+    torch.cuda.synchronize()
+    seq1 = c.seq()
+    assert c.signal_read() == (seq1, 0)
+    c.signal_post(41)
+    c.allreduce(0, 0, 1 << 20, torch.bfloat16, 0.5, algo=2)
+    torch.cuda.synchronize()
+    assert c.signal_read() == (c.seq(), 41) and c.seq() == seq1 + 1
+    wait_ns, launches, run_ns = c.stats(reset=True)
+    assert launches == 2 and 0 < run_ns < 10 ** 9 and 0 <= wait_ns <= run_ns
+    assert c.stats() == (0, 0, 0)
     c.close()

@@ -14,7 +14,8 @@ import torch
 from dist_utils import (get_rank, is_distributed_activated, is_rank0, log_rank0, maybe_cleanup_distributed,
                         maybe_init_distributed)
 from pyrecover.checkpoint import (load_ckpt_distributed, load_ckpt_vanilla, save_ckpt_distributed,
-                                  save_ckpt_vanilla, wait_for_checkpoints)
+                                  save_ckpt_vanilla, take_durable_checkpoint_time, wait_for_checkpoints)
+from pyrecover.resubmit import setup_resubmission
 from pyrecover.timelimit import TimeAwarePolicy
 from pyrecover_b200.trainer import Trainer, model_args_from_cli
 from pyrecover_b200.workload import SyntheticTokens
@@ -125,6 +126,18 @@ def train(args):
             log_rank0("Warning: SLURM_JOB_END_TIME is not set. Time-check logic will be skipped.")
         log_rank0(f"SLURM_JOB_END_TIME: {policy.end_time}")
 
+    # SLURM's pre-termination signal (#SBATCH --signal=USR1@<s>) or a plain SIGTERM: stop like the time-aware
+    # policy does (final checkpoint, clean exit) and, when a command is given, queue the continuation job
+    resub = None
+    if args.resubmit_command is not None:
+        import shlex
+        resub = setup_resubmission(shlex.split(args.resubmit_command) or None)
+        log_rank0(f"Resubmission on SIGUSR1/SIGTERM armed: {args.resubmit_command or '(stop only)'}")
+    stop_enabled = policy is not None or resub is not None
+    grad_sync = trainer.grad_sync            # K1 communicator (CUDA, world > 1): carries the stop decision
+    if policy is not None and grad_sync is not None:
+        policy.extra_iterations = grad_sync.STOP_LAG      # the decision takes effect that many steps later
+
     def ckpt_path(step, final=False):
         name = f"ckpt_{step}" + ("_final" if final else "") + ("" if sharded else ".pt")
         return exp_dir / name
@@ -150,17 +163,28 @@ def train(args):
     if is_distributed_activated() and world_size > 1:
         torch.distributed.barrier()
 
-    should_stop = False
-    stop_flag = torch.zeros(1, dtype=torch.int32, device=device) if world_size > 1 else None
+    should_stop = stop_posted = False
+    stop_flag = torch.zeros(1, dtype=torch.int32, device=device) if world_size > 1 and grad_sync is None else None
     ntokens = ntraining_tokens = 0
     time_last_log = time.perf_counter()
     log_rank0("Starting training!")
     while train_step < args.training_steps:
         train_step += 1
-        if policy is not None and is_rank0() and policy.should_stop():
+        if policy is not None:
+            durable = take_durable_checkpoint_time()       # an asynchronous write finished since the last look
+            if durable is not None and policy.observe_checkpoint(durable):
+                log_rank0(f"Updated max_ckpt_time: {policy.max_ckpt_time} (durable time of the previous checkpoint)")
+        if policy is not None and is_rank0() and not should_stop and policy.should_stop():
             should_stop = True
             log_rank0(f"[TIME CHECK] Remaining time ({policy.time_left():.2f}s) < threshold "
                       f"({policy.threshold:.2f}s). should_stop set to True.")
+        if resub is not None and is_rank0() and resub.stop_requested and not should_stop:
+            should_stop = True
+            log_rank0("[SIGNAL] termination signal received. should_stop set to True.")
+        if grad_sync is not None and stop_enabled and should_stop and not stop_posted and is_rank0():
+            at = grad_sync.request_stop()          # rides in this step's gradient exchange: no collective, no sync
+            stop_posted = True
+            log_rank0(f"[STOP] every rank stops after optimizer step {at} of this run")
         iter_start = time.perf_counter()
         if args.profile and args.profile_step_start == train_step and use_cuda:
             torch.cuda.cudart().cudaProfilerStart()
@@ -177,6 +201,8 @@ def train(args):
         if train_step == 1 or train_step % args.logging_frequency == 0:
             dt = time.perf_counter() - time_last_log
             tps = ntokens / dt
+            if hasattr(optimizer, "check_finite"):
+                optimizer.check_finite()           # non-finite gradient norm (clipping on): raise like the reference
             log_rank0(f"Epoch: {epoch} | Step: {train_step} | Loss: {loss.item():.2f} | Tokens per second: {tps:.2f} | "
                       f"Training tokens per second (%): {100 * (ntraining_tokens / dt) / tps:.2f} | "
                       f"MFU (%): {100 * num_flop_per_token * tps / H100_PEAK_FLOPS:.2f} | "
@@ -199,15 +225,22 @@ def train(args):
                 log_rank0(f"Updated max_ckpt_time: {policy.max_ckpt_time}")
             log_rank0(f"Checkpoint store completed in {dt:.2f} seconds")
 
-        if world_size > 1 and policy is not None:
-            # rank 0 decides (reference train.py:342-346); only paid when the policy is on
-            stop_flag.fill_(int(should_stop))
-            torch.distributed.broadcast(stop_flag, src=0)
-            should_stop = bool(stop_flag.item())
-        if policy is not None and should_stop:
+        stop_now = should_stop
+        if world_size > 1 and stop_enabled:
+            if grad_sync is not None:
+                stop_now = grad_sync.stop_due()        # rank 0's word, forwarded by K1's begin barrier
+            else:
+                # host path (CPU / gloo): rank 0 decides and broadcasts, as the reference (train.py:342-346)
+                stop_flag.fill_(int(should_stop))
+                torch.distributed.broadcast(stop_flag, src=0)
+                stop_now = should_stop = bool(stop_flag.item())
+        if stop_enabled and stop_now:
             log_rank0(f"[TIME CHECK] Saving final checkpoint to {ckpt_path(train_step, final=True)} before exit.")
-            dt = store(train_step, epoch, final=True)
+            t0 = time.perf_counter()
+            store(train_step, epoch, final=True)
             wait_for_checkpoints()
+            dt = time.perf_counter() - t0
+            ckpt_store_total += dt
             log_rank0(f"[TIME CHECK] Final checkpoint store completed in {dt:.2f} seconds")
             break
         if args.profile and args.profile_step_end == train_step and use_cuda:

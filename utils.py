@@ -73,6 +73,10 @@ _ADDITIVE_FLAGS = [
                               help="clip the global gradient norm to --grad-max-norm (the call the reference left "
                                    "commented out at train.py:271-272), folded into the optimizer kernel")),
     ("--sync-checkpoints", dict(action="store_true", help="wait for each checkpoint to be durable before continuing")),
+    ("--resubmit-command", dict(type=str, default=None,
+                                help="arm pyrecover.setup_resubmission: on SIGUSR1/SIGTERM write the _final checkpoint and "
+                                     "exit; a non-empty value (e.g. 'sbatch submit-training-simple.sh --continue') is run "
+                                     "once by rank 0 to queue the continuation job, '' only stops")),
 ]
 
 
