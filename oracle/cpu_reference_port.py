@@ -238,9 +238,12 @@ def run_ddp(preset: str, full_seq: int, steps: int, warmup: int, world: int, fus
     threads = max(1, cores // world)
     port = _free_port()
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    # the children are a job of their own: none of torchrun's variables may leak into them
+    # (TORCHELASTIC_USE_AGENT_STORE alone makes every rank look for a store that the agent hosts)
     env = {k: v for k, v in os.environ.items()
-           if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS",
-                        "GROUP_RANK", "ROLE_RANK", "LOCAL_WORLD_SIZE", "TORCHELASTIC_RUN_ID")}
+           if not k.startswith("TORCHELASTIC_") and
+           k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS", "GROUP_RANK",
+                     "GROUP_WORLD_SIZE", "ROLE_RANK", "ROLE_NAME", "ROLE_WORLD_SIZE", "LOCAL_WORLD_SIZE")}
     env["CUDA_VISIBLE_DEVICES"] = ""                        # the CPU arm must not touch a GPU
     env["OMP_NUM_THREADS"] = str(threads)
     with tempfile.TemporaryDirectory(prefix="pr_cpu_ddp_") as tmp:
@@ -249,7 +252,15 @@ def run_ddp(preset: str, full_seq: int, steps: int, warmup: int, world: int, fus
                                    str(threads), preset, str(full_seq), str(steps), str(warmup), str(int(fused)),
                                    str(budget_s_per_step), str(max_seconds), result_path], cwd=root, env=env)
                  for r in range(world)]
-        codes = [p.wait() for p in procs]
+        deadline = time.perf_counter() + max(600.0, 6 * max_seconds)      # never hang the caller
+        codes = []
+        for p in procs:
+            try:
+                codes.append(p.wait(timeout=max(1.0, deadline - time.perf_counter())))
+            except subprocess.TimeoutExpired:
+                for q in procs:
+                    q.kill()
+                raise RuntimeError("CPU DDP arm: workers did not finish in time")
         if any(codes):
             raise RuntimeError(f"CPU DDP arm: worker exit codes {codes}")
         with open(result_path) as f:

@@ -19,6 +19,7 @@ Both are a single launch here.
 """
 from __future__ import annotations
 
+import time
 from typing import Any, Dict, Iterable, List, Optional
 
 import torch
@@ -54,6 +55,8 @@ class B200AdamW(torch.optim.Optimizer):
         self._step_tensors: List[torch.Tensor] = []
         self._plans: List[Optional[K.AdamWPlan]] = []
         self.in_place_grads = True       # False: always gather gradients into the flat g arena first
+        self.step_period_s: Optional[float] = None     # smoothed host time between step() calls (the snapshot sizes its grid by it)
+        self._last_step_t: Optional[float] = None
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad,
                         maximize=maximize, foreach=foreach, capturable=capturable,
                         differentiable=differentiable, fused=fused, decoupled_weight_decay=True)
@@ -138,6 +141,18 @@ class B200AdamW(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
+        now = time.perf_counter()
+        if self._last_step_t is not None:
+            dt = now - self._last_step_t
+            if self.step_period_s is None:
+                self.step_period_s = dt
+            elif dt < 2.5 * self.step_period_s:         # a pause (logging sync, a blocking save, evaluation) is not a step
+                self.step_period_s = 0.8 * self.step_period_s + 0.2 * dt
+            else:
+                self._period_outliers = getattr(self, "_period_outliers", 0) + 1
+                if self._period_outliers >= 8:          # the cadence really changed
+                    self.step_period_s, self._period_outliers = dt, 0
+        self._last_step_t = now
         fence = getattr(self, "_snapshot_fence", None)
         if fence is not None:      # a checkpoint snapshot may still be reading the live arenas
             torch.cuda.current_stream().wait_event(fence)

@@ -42,7 +42,23 @@ ALIGN = 256
 COPY_CHUNK = 64 << 20
 _M64 = (1 << 64) - 1
 SHARD_FORMAT = 1
-PACK_BLOCKS = int(os.environ.get("PYRECOVER_B200_PACK_BLOCKS", "32"))
+# Grid of the bulk-copy pack kernel.  It runs on a side stream beside the next forward + backward and only has
+# to be done before the next optimizer step, so it is spread thin: measured on B200 (1 B model, 6 GB image,
+# 25 ms step) the stall of the training stream is 1.2 ms with 8 CTAs (the pack then takes 18 ms), 2.8 ms with
+# 16-32 and 3.5 ms with 64-148 -- a few CTAs ride in the SMs the GEMM waves leave idle, more displace them.
+# One CTA moves ~85 GB/s (read + write).  PYRECOVER_B200_PACK_BLOCKS fixes the grid; otherwise it is sized so
+# that the pack takes PACK_STEP_FRACTION of the step period the optimizer observes (15 ms when unknown).
+PACK_BLOCKS = int(os.environ.get("PYRECOVER_B200_PACK_BLOCKS", "0"))
+PACK_STEP_FRACTION = 0.7
+PACK_CTA_GBS = 85.0
+
+
+def pack_blocks_for(image_bytes: int, step_period_s: Optional[float]) -> int:
+    if PACK_BLOCKS > 0:
+        return PACK_BLOCKS
+    target = PACK_STEP_FRACTION * step_period_s if step_period_s else 0.015
+    blocks = int(2.0 * image_bytes / (PACK_CTA_GBS * 1e9 * max(target, 1e-4)) + 0.999)
+    return max(4, min(148, blocks))
 
 
 def _round_up(x: int, a: int) -> int:
@@ -75,7 +91,7 @@ class Image:
         self.sum_host = torch.zeros(2, dtype=torch.int64).pin_memory()
         self.e_copied: Optional[torch.cuda.Event] = None
 
-    def stage(self, side: torch.cuda.Stream):
+    def stage(self, side: torch.cuda.Stream, step_period_s: Optional[float] = None):
         """Runs on `side`, ordered after the work already queued on the training stream: pack
         (+PR-SUM64) into the staging image.  Returns e_read: once it has fired the live tensors
         may be modified again (the caller fences the next optimizer step on it -- forward and
@@ -93,10 +109,10 @@ class Image:
             self.sum_dev.zero_()
         e_read = torch.cuda.Event()
         if self.staging is not None:
-            # the bulk-copy (TMA-staged) pack kernel on a bounded number of CTAs: it runs beside the next
-            # forward pass and should take few SMs from it (PYRECOVER_B200_PACK_BLOCKS, 0 = kernel default)
+            # the bulk-copy (TMA-staged) pack kernel on a bounded number of CTAs (pack_blocks_for)
             torch.cuda.nvtx.range_push("ckpt_pack")
-            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side, max_blocks=PACK_BLOCKS)
+            self.pack_blocks = pack_blocks_for(self.image_bytes, step_period_s)
+            self.plan.pack(self.staging.data_ptr(), self.sum_dev, stream=side, max_blocks=self.pack_blocks)
             torch.cuda.nvtx.range_pop()
             e_read.record(side)
         else:                                    # direct: copy engines read the live tensors, all at once
@@ -442,10 +458,11 @@ class Snapshotter:
         self._check_exchange()
         self.wait()                          # the pinned arena is about to be overwritten
         img = self.full()
-        e_read, e_copied = img.stage(self.side)
+        e_read, e_copied = img.stage(self.side, getattr(self.optimizer, "step_period_s", None))
         self._fence_optimizer(e_read)
         path = str(path)
-        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
+        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes,
+                           "pack_blocks": getattr(img, "pack_blocks", None)}
         self._durable_reported = False
 
         def work():
@@ -514,14 +531,15 @@ class Snapshotter:
         self._check_exchange()
         self.wait()
         img = self.shard(rank, world)
-        e_read, e_copied = img.stage(self.side)
+        e_read, e_copied = img.stage(self.side, getattr(self.optimizer, "step_period_s", None))
         self._fence_optimizer(e_read)
         self._durable_reported = False
         small_state = _to_cpu(small_state)
         if rank == 0:
             small_state["layout"] = self.tensor_layout()
         d = Path(dirpath)
-        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes}
+        self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes,
+                           "pack_blocks": getattr(img, "pack_blocks", None)}
 
         def work():
             t1 = time.perf_counter()

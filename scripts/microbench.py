@@ -192,7 +192,8 @@ def main():
     garena = torch.zeros(chunk * len(gchunks), dtype=torch.bfloat16, device=dev)
     ms, best = timeit(lambda: aplan.gather(gchunks, garena), a.iters)
     row("pr_gather_grads (2 B r + 2 B w)", ms, best, 4 * n)
-    ms, best = timeit(lambda: torch._foreach_copy_(list(torch.split(garena, chunk)), gchunks), a.iters)
+    gviews = [garena[i * chunk:i * chunk + c.numel()] for i, c in enumerate(gchunks)]
+    ms, best = timeit(lambda: torch._foreach_copy_(gviews, gchunks), a.iters)
     row("torch._foreach_copy_ same tensors", ms, best, 4 * n)
     del gchunks, garena
     # D2H of the image into the pinned arena (PCIe leg)

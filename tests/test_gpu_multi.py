@@ -153,3 +153,50 @@ def test_two_gpu_matches_vanilla_and_sharded(tmp_path):
         assert torch.equal(t, V["model"][k]), k
     for i, p in enumerate(m.parameters()):
         assert torch.equal(o.state[p]["exp_avg_sq"], V["optimizer"]["state"][i]["exp_avg_sq"])
+
+
+def test_two_gpu_overlap_many_buckets_resume_weight_equality(tmp_path):
+    """"overlap" with buckets small enough that the tiny model is exchanged in many launches under backward
+    (one learned trigger hook per bucket): straight vs resumed runs still end bit-identical, and equal to the
+    single-launch "fused" run (same slices of the same sums, only cut per bucket)."""
+    _need(2)
+    env = {"PYRECOVER_B200_BUCKET_BYTES": str(1 << 20), "PR_COMM_MULTICAST": "0"}
+    extra = ("--grad-sync", "overlap")
+    _launch(tmp_path, "straight", 20, 2, extra, env)
+    _launch(tmp_path, "resumed", 10, 2, extra, env)
+    _launch(tmp_path, "resumed", 20, 2, extra + ("--resume-from-checkpoint", "latest"), env)
+    _launch(tmp_path, "fused", 20, 2, ("--grad-sync", "fused"), {"PR_COMM_MULTICAST": "0"})
+    A = torch.load(tmp_path / "straight" / "ckpt_20.pt", map_location="cpu")
+    B = torch.load(tmp_path / "resumed" / "ckpt_20.pt", map_location="cpu")
+    C = torch.load(tmp_path / "fused" / "ckpt_20.pt", map_location="cpu")
+    for k in A["model"]:
+        assert torch.equal(A["model"][k], B["model"][k]), k
+        assert torch.equal(A["model"][k], C["model"][k]), k
+    for i in A["optimizer"]["state"]:
+        assert torch.equal(A["optimizer"]["state"][i]["exp_avg"], B["optimizer"]["state"][i]["exp_avg"])
+        assert torch.equal(A["optimizer"]["state"][i]["exp_avg_sq"], C["optimizer"]["state"][i]["exp_avg_sq"])
+
+
+@pytest.mark.parametrize("mode", ["fused", "overlap"])
+def test_two_gpu_timeaware_stop_rides_in_the_exchange(tmp_path, mode):
+    """Time-aware stop at W = 2 (reference train.py:163-190, 223-232, 342-375) with the decision carried by
+    K1's begin barrier instead of a per-step broadcast + .item(): with a simulated SLURM_JOB_END_TIME both
+    ranks stop after the SAME step, write ckpt_<step>_final as a complete sharded directory, and a resumed run
+    continues from it.  PYRECOVER_B200_SYNC_DEBUG=1 makes train.py run the steady-state steps under
+    torch.cuda.set_sync_debug_mode("error"): any host<->device synchronisation in the loop fails the run."""
+    _need(2)
+    import re
+    import time
+    env = {"SLURM_JOB_END_TIME": str(int(time.time()) + 45), "PYRECOVER_B200_SYNC_DEBUG": "1"}
+    extra = ("--grad-sync", mode, "--timeaware-checkpointing", "--use-torch-distributed-ckpt", "--default-iter-time", "0.5",
+             "--default-ckpt-time", "2", "--checkpoint-frequency", "-1", "--logging-frequency", "1000000")
+    r = _launch(tmp_path, "ta", 100000, 2, extra, env)
+    out = r.stdout + r.stderr
+    finals = sorted((tmp_path / "ta").glob("ckpt_*_final"))
+    assert len(finals) == 1, out[-3000:]
+    step = int(re.search(r"ckpt_(\d+)_final", finals[0].name).group(1))
+    assert step > 10 and "[STOP] every rank stops after optimizer step" in out
+    assert (finals[0] / "COMPLETE_00000").exists() and (finals[0] / "COMPLETE_00001").exists()
+    r2 = _launch(tmp_path, "ta", step + 5, 2, ("--grad-sync", mode, "--use-torch-distributed-ckpt", "--resume-from-checkpoint",
+                                               "latest", "--checkpoint-frequency", "-1"))
+    assert f"step {step})" in (r2.stdout + r2.stderr)

@@ -163,6 +163,8 @@ def train(args):
     if is_distributed_activated() and world_size > 1:
         torch.distributed.barrier()
 
+    # test aid: fail the run on ANY host<->device synchronisation inside a steady-state step
+    sync_debug = use_cuda and __import__("os").environ.get("PYRECOVER_B200_SYNC_DEBUG") == "1"
     should_stop = stop_posted = False
     stop_flag = torch.zeros(1, dtype=torch.int32, device=device) if world_size > 1 and grad_sync is None else None
     ntokens = ntraining_tokens = 0
@@ -190,6 +192,10 @@ def train(args):
             torch.cuda.cudart().cudaProfilerStart()
             torch.autograd.profiler.emit_nvtx(record_shapes=True).__enter__()
 
+        logging_step = train_step == 1 or train_step % args.logging_frequency == 0
+        strict = sync_debug and train_step > 3 and not logging_step and csv_writer is None
+        if strict:
+            torch.cuda.set_sync_debug_mode("error")
         input_ids, labels = fetch(train_step)
         ntokens += global_batch_size * args.sequence_length
         ntraining_tokens += int(labels.ne(-100).sum()) * world_size
@@ -198,7 +204,7 @@ def train(args):
         if csv_writer is not None:
             csv_writer.writerow([train_step, loss.item()])
             csv_file.flush()
-        if train_step == 1 or train_step % args.logging_frequency == 0:
+        if logging_step:
             dt = time.perf_counter() - time_last_log
             tps = ntokens / dt
             if hasattr(optimizer, "check_finite"):
@@ -215,6 +221,17 @@ def train(args):
             if train_step % args.logging_frequency == 0:
                 log_rank0(f"Current buffer_time: {policy.buffer_time}")
 
+        stop_now = should_stop
+        if world_size > 1 and stop_enabled:
+            if grad_sync is not None:
+                stop_now = grad_sync.stop_due()        # rank 0's word, forwarded by K1's begin barrier
+            else:
+                # host path (CPU / gloo): rank 0 decides and broadcasts, as the reference (train.py:342-346)
+                stop_flag.fill_(int(should_stop))
+                torch.distributed.broadcast(stop_flag, src=0)
+                stop_now = should_stop = bool(stop_flag.item())
+        if strict:
+            torch.cuda.set_sync_debug_mode("default")
         saved_this_step = False
         if args.checkpoint_frequency != -1 and train_step % args.checkpoint_frequency == 0:
             log_rank0(f"Saving checkpoint to {ckpt_path(train_step)}")
@@ -225,15 +242,6 @@ def train(args):
                 log_rank0(f"Updated max_ckpt_time: {policy.max_ckpt_time}")
             log_rank0(f"Checkpoint store completed in {dt:.2f} seconds")
 
-        stop_now = should_stop
-        if world_size > 1 and stop_enabled:
-            if grad_sync is not None:
-                stop_now = grad_sync.stop_due()        # rank 0's word, forwarded by K1's begin barrier
-            else:
-                # host path (CPU / gloo): rank 0 decides and broadcasts, as the reference (train.py:342-346)
-                stop_flag.fill_(int(should_stop))
-                torch.distributed.broadcast(stop_flag, src=0)
-                stop_now = should_stop = bool(stop_flag.item())
         if stop_enabled and stop_now:
             log_rank0(f"[TIME CHECK] Saving final checkpoint to {ckpt_path(train_step, final=True)} before exit.")
             t0 = time.perf_counter()
