@@ -53,7 +53,9 @@ def parse():
     ap.add_argument("--preset", type=str, default="1b", choices=["tiny", "1b", "8b"])
     ap.add_argument("--seq", type=int, default=2048)
     ap.add_argument("--grad-sync", type=str, default=None, choices=[None, "replicated", "fused", "overlap"],
-                    help="default: overlap (gather + fused exchange/update per bucket under backward)")
+                    help="default: fused below 4 GPUs (the P2P kernels need every SM to fill the links, so they run after "
+                         "backward), overlap from 4 up (the NVSwitch-multicast kernels need a few dozen CTAs and run per "
+                         "bucket under backward)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around timed leg 1 (for ncu --profile-from-start off)")
     ap.add_argument("--no-ckpt", action="store_true", help="skip the in-region checkpoint snapshot and the stall measurement")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -435,7 +437,7 @@ def run_b200(a):
     from pyrecover_b200.trainer import Trainer
     from pyrecover_b200.workload import MODEL_PRESETS, SyntheticTokens, Transformer, preset_args
 
-    grad_sync_mode = a.grad_sync or "overlap"
+    grad_sync_mode = a.grad_sync or ("overlap" if world >= 4 else "fused")
     vocab = MODEL_PRESETS[a.preset][5]
     torch.manual_seed(0)
     torch.set_default_dtype(torch.bfloat16)

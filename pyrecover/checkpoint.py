@@ -269,9 +269,11 @@ def save_ckpt_distributed(
 ) -> str:
     """Sharded save into the directory `checkpoint_path`: every rank stores 1/W of the state.
 
-    B200 path: rank r packs its element slice of (p, m, v) -- the reduce-scatter slice of the
-    gradient exchange -- into `shard_<r>.bin`; rank 0 adds `meta.pt`.  Host path (CPU/gloo): the
-    reference's torch.distributed.checkpoint call."""
+    B200 path: rank r packs its element slices of (p, m, v) -- the reduce-scatter slices of the
+    gradient exchange -- into `__<r>_0.distcp`, framed box by box as torch.distributed.checkpoint items,
+    and rank 0 writes `.metadata` last: the directory is what the reference's dist_cp.save call
+    (pyrecover/checkpoint.py:254-274) produces, written without re-replicating or re-serialising anything
+    (pyrecover_b200/dcpfile.py).  Host path (CPU/gloo): the reference's torch.distributed.checkpoint call."""
     fast = _is_b200(optimizer)
     if is_distributed:
         _save_barrier(fast)
@@ -351,7 +353,9 @@ def load_ckpt_distributed(
         if checkpoint_path is None:
             raise RuntimeError(f"No checkpoint found in {experiment_dir}")
     checkpoint_path = str(checkpoint_path)
-    native = any(Path(checkpoint_path).glob("shard_*.json"))
+    native = any(Path(checkpoint_path).glob("b200_*.json")) or any(Path(checkpoint_path).glob("shard_*.json"))
+    if native and not _is_b200(optimizer) and (Path(checkpoint_path) / ".metadata").exists():
+        native = False      # a stock optimizer: our directories are torch.distributed.checkpoint directories too
     if native:
         if not _is_b200(optimizer):
             raise RuntimeError(f"{checkpoint_path} is a pyrecover_b200 sharded checkpoint; it loads into a "
@@ -361,7 +365,7 @@ def load_ckpt_distributed(
             checkpoint_path, verify, rank=dist.get_rank() if is_distributed else 0, world=world,
             grad_sync=getattr(optimizer, "_grad_sync", None))
         for g, saved in zip(optimizer.param_groups, small["param_groups"]):
-            g.update(saved)
+            g.update({k: v for k, v in saved.items() if k != "params"})
         for gi, s in enumerate(small["opt_steps"]):
             optimizer.set_step(gi, s)
         if getattr(optimizer, "_grad_sync", None) is not None:
@@ -409,7 +413,7 @@ def get_latest_checkpoint(checkpoint_dir: str, distributed: bool = False) -> Opt
     if distributed:
         items = [d for d in base.glob("ckpt_*") if d.is_dir() and _dir_complete(d)]
     else:
-        items = [f for f in base.glob("**/*.pt") if f.is_file() and f.name != "meta.pt"
+        items = [f for f in base.glob("**/*.pt") if f.is_file() and f.name not in ("meta.pt", "b200_meta.pt")
                  and not f.name.startswith("rng_")]
     if not items:
         return None

@@ -4,10 +4,12 @@ Keeps checkpoints written by the B200 path portable to stock tooling, and the ot
 
     python -m pyrecover.convert SRC DST --to vanilla|dcp
 
-SRC is any of: a vanilla `.pt` file (ours or one written by the reference's save_ckpt_vanilla,
-pyrecover/checkpoint.py:25-105), one of our sharded directories (`shard_<r>.bin` + `meta.pt`), or a
-torch.distributed.checkpoint directory written by the reference's save_ckpt_distributed (:218-297;
-needs --template-from to know the keys -- DCP loads into an existing state dict).
+SRC is a vanilla `.pt` file (ours or one written by the reference's save_ckpt_vanilla,
+pyrecover/checkpoint.py:25-105) or one of our sharded directories (`__<r>_0.distcp` + `b200_<r>.json` +
+`b200_meta.pt`; the older `shard_<r>.bin` + `meta.pt` layout is still read).  Our sharded directories ARE
+torch.distributed.checkpoint directories already (stock `dist_cp.load` opens them), so `--to dcp` matters
+for vanilla sources.  A DCP directory written by stock torch is not a source here: DCP can only be loaded
+into an existing state dict, which `load_ckpt_distributed` does.
   --to vanilla : one torch.load-able file with the reference's top-level keys
                  (epoch, step, model, optimizer, lr_scheduler[, sampler_state], rng_state)
   --to dcp     : a torch.distributed.checkpoint directory with exactly the keys the reference's
@@ -35,20 +37,25 @@ _DTYPES = {"bfloat16": torch.bfloat16, "float32": torch.float32, "float16": torc
 def _read_sharded(d: Path) -> Dict[str, Any]:
     """Assemble the full image from every shard (any world size) and rebuild the reference's state
     dict from the layout table rank 0 stored in meta.pt."""
-    infos = [json.loads(p.read_text()) for p in sorted(d.glob("shard_*.json"))]
+    sides = sorted(d.glob("b200_*.json"))
+    native_dcp = bool(sides)              # format 2: the shard files are torch.distributed.checkpoint files
+    if not sides:
+        sides = sorted(d.glob("shard_*.json"))
+    infos = [json.loads(p.read_text()) for p in sides]
     if not infos:
         raise RuntimeError(f"No checkpoint shards found in {d}")
     world = infos[0]["world"]
-    if len(infos) != world or any(not (d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos):
+    complete = (d / ".metadata").exists() if native_dcp else all((d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos)
+    if len(infos) != world or not complete:
         raise RuntimeError(f"Sharded checkpoint {d} is incomplete ({len(infos)} of {world} shards)")
-    meta = torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
+    meta = torch.load(str(d / ("b200_meta.pt" if native_dcp else "meta.pt")), map_location="cpu", weights_only=False)
     layout = meta.get("layout")
     if layout is None:
         raise RuntimeError(f"{d}/meta.pt carries no tensor layout (written by an older build): load it on a GPU "
                            "with load_ckpt_distributed and re-save")
     image = np.zeros(int(infos[0]["full_image_bytes"]), dtype=np.uint8)
     for info in infos:
-        with open(d / f"shard_{info['rank']:05d}.bin", "rb") as f:
+        with open(d / (info["file"] if native_dcp else f"shard_{info['rank']:05d}.bin"), "rb") as f:
             for goff, n, loff in info["pieces"]:
                 f.seek(loff)
                 got = f.readinto(memoryview(image)[goff:goff + n])
@@ -89,7 +96,7 @@ def load_state_cpu(src: str) -> Dict[str, Any]:
     p = Path(src)
     if p.is_file():
         return torch.load(str(p), map_location="cpu", weights_only=False)
-    if any(p.glob("shard_*.json")):
+    if any(p.glob("b200_*.json")) or any(p.glob("shard_*.json")):
         return _read_sharded(p)
     raise RuntimeError(f"{src}: neither a checkpoint file nor a pyrecover_b200 sharded directory")
 

@@ -304,9 +304,11 @@ def write_archive(path: str, pickle_bytes: bytes, records: Sequence[Tuple[str, A
                                        if b"/data/" in e.name}, "bytes": nbytes}
 
 
-def write_raw(path: str, chunks, fsync: bool = True, direct: Optional[bool] = None) -> int:
-    """Stream bytes-likes to `<path>.tmp` and rename (the sharded format's shard_<r>.bin): O_DIRECT for
-    the 4096-aligned bulk of every aligned buffer, buffered writes otherwise.  Returns the byte count."""
+def write_raw(path: str, chunks, fsync: bool = True, direct: Optional[bool] = None, observer=None, epilogue=None) -> int:
+    """Stream bytes-likes to `<path>.tmp` and rename (a rank's shard file): O_DIRECT for the
+    4096-aligned bulk of every aligned buffer, buffered writes otherwise.  Returns the byte count.
+    observer(file_offset, memoryview) sees every chunk as it goes out (checksums); epilogue(fd, end_offset)
+    runs before the fsync and may pwrite anywhere in the file -- it returns the final file size."""
     path = str(path)
     tmp = path + ".tmp"
     fd = os.open(tmp, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
@@ -321,6 +323,8 @@ def write_raw(path: str, chunks, fsync: bool = True, direct: Optional[bool] = No
         for chunk in chunks:
             mv = memoryview(chunk).cast("B")
             n = mv.nbytes
+            if observer is not None:
+                observer(off, mv)
             bulk = n - n % DIRECT_ALIGN
             if dfd >= 0 and bulk and off % DIRECT_ALIGN == 0 and _buffer_address(mv) % DIRECT_ALIGN == 0:
                 try:
@@ -333,6 +337,8 @@ def write_raw(path: str, chunks, fsync: bool = True, direct: Optional[bool] = No
             else:
                 _pwrite_all(fd, mv, off)
             off += n
+        if epilogue is not None:
+            off = epilogue(fd, off)
         if fsync:
             os.fsync(fd)
     except BaseException:

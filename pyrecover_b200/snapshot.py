@@ -35,13 +35,14 @@ from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
+from . import dcpfile as DCP
 from . import kernels as K
 from . import ptfile as PT
 
 ALIGN = 256
 COPY_CHUNK = 64 << 20
 _M64 = (1 << 64) - 1
-SHARD_FORMAT = 1
+SHARD_FORMAT = 2        # 2: torch.distributed.checkpoint directory written natively (dcpfile.py); 1: raw shard_<r>.bin (still read)
 # Grid of the bulk-copy pack kernel.  It runs on a side stream beside the next forward + backward and only has
 # to be done before the next optimizer step, so it is spread thin: measured on B200 (1 B model, 6 GB image,
 # 25 ms step) the stall of the training stream is 1.2 ms with 8 CTAs (the pack then takes 18 ms), 2.8 ms with
@@ -198,6 +199,7 @@ class Snapshotter:
         self._stub_cache: Dict[Any, PT.TensorStub] = {}
         self._layout: Optional[Dict[str, Any]] = None
         self._skeleton: Optional[Dict[str, Any]] = None
+        self._dcp_plans: Dict[Any, Any] = {}
         self.last_stats: Dict[str, Any] = {}
         self.durable_s: Optional[float] = None      # save_* call -> file renamed, of the last FINISHED write
         self._durable_reported = True
@@ -265,20 +267,32 @@ class Snapshotter:
                 runs.append((p.global_off, p.nbytes))
         return runs
 
+    def dcp_plan(self, rank: int, world: int):
+        """(items, tensor-part bytes) of rank `rank`'s `__<rank>_0.distcp`: every box of every tensor the rank
+        owns, framed as a torch archive at a fixed file offset (dcpfile.plan_rank).  Static for the job."""
+        key = (rank, world)
+        if key not in self._dcp_plans:
+            # the reference's keys: its model is DDP-wrapped whenever world > 1 ("model.module.<name>")
+            table = DCP.tensor_table(self.tensor_layout(), "module." if world > 1 else "")
+            self._dcp_plans[key] = DCP.plan_rank(table, self.shard_pieces(rank, world))
+        return self._dcp_plans[key]
+
     def shard(self, rank: int, world: int) -> Image:
+        """This rank's image = the tensor part of its .distcp file: the pack kernel drops every owned box at
+        the offset its bytes have in the file; the framing around them is written by the host."""
         if self._shard is None or self._shard_key != (rank, world):
             if self._shard is not None:
                 self._shard.close()
-            pieces, off = [], 0
-            runs = self.shard_pieces(rank, world)
-            for p in self.full_pieces:
-                flat = p.tensor.reshape(-1).view(torch.uint8)
-                for goff, n in runs:
-                    if p.global_off <= goff < p.global_off + max(p.nbytes, 1):
-                        lo = goff - p.global_off
-                        pieces.append(Piece(flat[lo:lo + n], off, global_off=goff))
-                        off += _round_up(n, ALIGN)
-            self._shard = Image(pieces, off, self.device, self.mode == "staged")
+            items, nbytes = self.dcp_plan(rank, world)
+            flats = [(p.global_off, p.nbytes, p.tensor.reshape(-1).view(torch.uint8)) for p in self.full_pieces if p.nbytes]
+            pieces, k = [], 0
+            for it in items:                       # items and full_pieces are both ordered by image offset
+                while not (flats[k][0] <= it.global_off < flats[k][0] + flats[k][1]):
+                    k += 1
+                base, _, flat = flats[k]
+                lo = it.global_off - base
+                pieces.append(Piece(flat[lo:lo + it.nbytes], it.payload_off, global_off=it.global_off))
+            self._shard = Image(pieces, nbytes, self.device, self.mode == "staged")
             self._shard_key = (rank, world)
         return self._shard
 
@@ -524,19 +538,28 @@ class Snapshotter:
     # ------------------------------------------------------------------ sharded directory -
     def save_sharded(self, dirpath: str, small_state: Dict[str, Any], rank: int, world: int,
                      max_keep: int, blocking: bool = False) -> None:
-        """Every rank writes `shard_<rank>.bin` (its slice of p, m, v) + `shard_<rank>.json`;
-        rank 0 also writes `meta.pt` (python-side state) and rotates old directories.  The
-        directory is complete when `COMPLETE_<rank>` exists for every rank."""
+        """Every rank writes `__<rank>_0.distcp` -- its boxes of p, m, v as torch archives, straight from
+        the pinned image -- and a side-car `b200_<rank>.json` (PR-SUM64, where each box lies); rank 0 adds the
+        python-side items to its file, writes `b200_meta.pt` and, once every rank's side-car is there,
+        `.metadata`: the directory is then a torch.distributed.checkpoint checkpoint that stock
+        `dist_cp.load` and the reference's load_ckpt_distributed (pyrecover/checkpoint.py:300-368) open, and it
+        is complete exactly when `.metadata` exists (as with dist_cp.save)."""
         t0 = time.perf_counter()
         self._check_exchange()
         self.wait()
         img = self.shard(rank, world)
+        items, nbytes = self.dcp_plan(rank, world)
         e_read, e_copied = img.stage(self.side, getattr(self.optimizer, "step_period_s", None))
         self._fence_optimizer(e_read)
         self._durable_reported = False
         small_state = _to_cpu(small_state)
+        n_params = sum(len(g["params"]) for g in self.optimizer.param_groups)
         if rank == 0:
             small_state["layout"] = self.tensor_layout()
+            nxt = 0
+            for g, live in zip(small_state["param_groups"], self.optimizer.param_groups):
+                g["params"] = list(range(nxt, nxt + len(live["params"])))
+                nxt += len(live["params"])
         d = Path(dirpath)
         self.last_stats = {"enqueue_s": time.perf_counter() - t0, "image_bytes": img.image_bytes,
                            "pack_blocks": getattr(img, "pack_blocks", None)}
@@ -547,19 +570,25 @@ class Snapshotter:
             e_copied.synchronize()
             self._check_exchange()
             t2 = time.perf_counter()
-            shard_path = d / f"shard_{rank:05d}.bin"
-            PT.write_raw(str(shard_path), img.drain(self.side))
-            A, B = img.checksum()
-            side = {"format": SHARD_FORMAT, "rank": rank, "world": world, "sum64": [A, B],
-                    "image_bytes": img.image_bytes, "full_image_bytes": self.full_bytes,
-                    "pieces": [[p.global_off, p.nbytes, p.img_off] for p in img.pieces]}
-            _write_text_atomic(d / f"shard_{rank:05d}.json", json.dumps(side))
+            small_flat = small_paths = None
             if rank == 0:
-                torch.save(small_state, str(d / "meta.pt.tmp"))
-                os.replace(str(d / "meta.pt.tmp"), str(d / "meta.pt"))
+                small_flat, small_paths = DCP.small_state_items(small_state, n_params)
+            placed = DCP.write_rank_file(str(d / DCP.rank_file(rank)), items, nbytes, img.drain(self.side), small_flat)
+            A, B = img.checksum()
+            side = {"format": SHARD_FORMAT, "rank": rank, "world": world, "sum64": [A, B], "step": small_state.get("step"),
+                    "image_bytes": img.image_bytes, "full_image_bytes": self.full_bytes, "file": DCP.rank_file(rank),
+                    "pieces": [[p.global_off, p.nbytes, p.img_off] for p in img.pieces]}
+            if rank == 0:
+                torch.save(small_state, str(d / "b200_meta.pt.tmp"))
+                os.replace(str(d / "b200_meta.pt.tmp"), str(d / "b200_meta.pt"))
             else:
                 torch.save({"rng_state": small_state.get("rng_state")}, str(d / f"rng_{rank:05d}.pt"))
-            _write_text_atomic(d / f"COMPLETE_{rank:05d}", str(world))
+            _write_text_atomic(d / f"b200_{rank:05d}.json", json.dumps(side))
+            if rank == 0:
+                _await_sidecars(d, world, small_state.get("step"))
+                plans = {r: self.dcp_plan(r, world)[0] for r in range(world)}
+                table = DCP.tensor_table(self.tensor_layout(), "module." if world > 1 else "")
+                DCP.write_metadata(str(d), DCP.build_metadata(table, plans, small_flat, small_paths, placed))
             self.durable_s = time.perf_counter() - t0
             if rank == 0:
                 rotate_dirs(d.parent, max_keep)
@@ -582,23 +611,32 @@ class Snapshotter:
         each shard's PR-SUM64."""
         self.wait()
         d = Path(dirpath)
-        sides = sorted(d.glob("shard_*.json"))
+        sides = sorted(d.glob("b200_*.json"))
+        native_dcp = bool(sides)
+        if not sides:
+            sides = sorted(d.glob("shard_*.json"))          # format 1 (raw shard files), still readable
         if not sides:
             raise RuntimeError(f"No checkpoint shards found in {d}")
         infos = [json.loads(s.read_text()) for s in sides]
         saved_world = infos[0]["world"]
-        if len(infos) != saved_world or any(not (d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos):
+        complete = (d / ".metadata").exists() if native_dcp else \
+            all((d / f"COMPLETE_{i['rank']:05d}").exists() for i in infos)
+        if len(infos) != saved_world or not complete:
             raise RuntimeError(f"Sharded checkpoint {d} is incomplete ({len(infos)} of {saved_world} shards)")
         if infos[0]["full_image_bytes"] != self.full_bytes:
             raise RuntimeError("checkpoint image layout differs from the live model")
-        if grad_sync is not None and world > 1 and saved_world == world and grad_sync.world == world \
+        meta_path = d / ("b200_meta.pt" if native_dcp else "meta.pt")
+
+        def shard_file(info):
+            return d / (info["file"] if native_dcp else f"shard_{info['rank']:05d}.bin")
+        if native_dcp and grad_sync is not None and world > 1 and saved_world == world and grad_sync.world == world \
                 and os.environ.get("PYRECOVER_B200_SLICE_LOAD", "1") != "0":
             self._load_own_shard(d, next(i for i in infos if i["rank"] == rank), rank, world, grad_sync, verify)
-            return torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
+            return torch.load(str(meta_path), map_location="cpu", weights_only=False)
         img = self.full()
         mv = img.host.view()
         for info in infos:
-            with open(d / f"shard_{info['rank']:05d}.bin", "rb", buffering=0) as f:
+            with open(shard_file(info), "rb", buffering=0) as f:
                 for goff, n, loff in info["pieces"]:
                     f.seek(loff)
                     _read_exact(f, mv[goff:goff + n], str(d))
@@ -611,7 +649,7 @@ class Snapshotter:
                     K.checksum_into(image[goff:goff + n], s, loff // 4)
                 if K._sum_to_ints(s) != tuple(info["sum64"]):
                     raise RuntimeError(f"Checksum mismatch for shard {info['rank']} of {d}")
-        return torch.load(str(d / "meta.pt"), map_location="cpu", weights_only=False)
+        return torch.load(str(meta_path), map_location="cpu", weights_only=False)
 
     def _load_own_shard(self, d: Path, info: Dict[str, Any], rank: int, world: int, grad_sync, verify: bool) -> None:
         import torch.distributed as dist
@@ -619,7 +657,7 @@ class Snapshotter:
         if info["image_bytes"] != img.image_bytes or \
                 [list(x) for x in info["pieces"]] != [[p.global_off, p.nbytes, p.img_off] for p in img.pieces]:
             raise RuntimeError(f"shard {rank} of {d} does not match this rank's slice layout")
-        with open(d / f"shard_{rank:05d}.bin", "rb", buffering=0) as f:
+        with open(d / info["file"], "rb", buffering=0) as f:
             _read_exact(f, img.host.view(0, img.image_bytes), str(d))
         got = img.restore()                        # H2D + unpack into the live slices + PR-SUM64
         if verify and tuple(info["sum64"]) != got:
@@ -683,6 +721,28 @@ def _read_exact(f, mv: memoryview, what: str) -> None:
         got += k
 
 
+def _await_sidecars(d: Path, world: int, step, timeout_s: Optional[float] = None) -> None:
+    """Rank 0's writer thread, before it writes `.metadata`: every rank's file is durable (each rank writes
+    its side-car after its .distcp has been renamed into place).  Ranks save the same step within a few
+    milliseconds of each other, so this normally returns at once."""
+    timeout_s = float(os.environ.get("PYRECOVER_B200_PEER_WRITE_TIMEOUT_S", "1800")) if timeout_s is None else timeout_s
+    deadline = time.monotonic() + timeout_s
+    missing = list(range(world))
+    while missing:
+        still = []
+        for r in missing:
+            try:
+                if json.loads((d / f"b200_{r:05d}.json").read_text()).get("step") != step:
+                    still.append(r)
+            except (OSError, ValueError):
+                still.append(r)
+        missing = still
+        if missing:
+            if time.monotonic() > deadline:
+                raise RuntimeError(f"sharded checkpoint {d}: ranks {missing} did not finish writing within {timeout_s:.0f} s")
+            time.sleep(0.02)
+
+
 def _write_text_atomic(path: Path, text: str) -> None:
     tmp = str(path) + ".tmp"
     with open(tmp, "w") as f:
@@ -704,7 +764,9 @@ def rotate_files(base: Path, max_keep: int) -> None:
     ordered by STEP NUMBER rather than lexicographically (ckpt_1000.pt sorts after ckpt_200.pt)."""
     if max_keep <= 0:
         return
-    files = sorted((x for x in base.glob("**/*.pt") if x.is_file()), key=_step_key)
+    # only files named like checkpoints: a sharded directory's b200_meta.pt / rng_<r>.pt living under the same
+    # experiment directory must never be "rotated" away (the reference removes any old *.pt)
+    files = sorted((x for x in base.glob("**/*.pt") if x.is_file() and _STEP_RE.match(x.name)), key=_step_key)
     for f in files[:-max_keep] if len(files) > max_keep else []:
         for side in ("", ".md5", ".b200sum"):
             try:

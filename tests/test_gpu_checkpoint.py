@@ -183,8 +183,11 @@ def test_reference_written_checkpoint_loads(cuda_lib, golden_dir, tmp_path):
 
 @pytest.mark.parametrize("world", [1, 2, 4])
 def test_sharded_save_load_roundtrip(cuda_lib, tmp_path, world):
-    """Every rank's shard written (here: one process plays all ranks in turn), then restored into
-    a fresh model: bit-exact; per-shard PR-SUM64 verified on the GPU; a flipped byte is caught."""
+    """Every rank's shard written (here: one process plays all ranks in turn, rank 0 last because it waits
+    for the others before it writes .metadata), then restored into a fresh model: bit-exact; per-shard
+    PR-SUM64 verified on the GPU; a flipped byte is caught.  The directory is a torch.distributed.checkpoint
+    checkpoint: stock dist_cp.load fills a CPU state dict with the same bits (the reference's
+    load_ckpt_distributed, pyrecover/checkpoint.py:352-356, is that call)."""
     import pyrecover
     from pyrecover import checkpoint as ck
     model, opt, sched = _build()
@@ -193,30 +196,51 @@ def test_sharded_save_load_roundtrip(cuda_lib, tmp_path, world):
     snap = ck._snapshotter(model, opt)
     small = {"epoch": 1, "step": 2, "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in opt.param_groups],
              "opt_steps": list(opt._steps), "rng_state": ck._rng_state(), "lr_scheduler": sched.state_dict()}
-    for r in range(world):
+    for r in reversed(range(world)):
         snap.save_sharded(str(d), small, r, world, max_keep=3, blocking=True)
-    assert pyrecover.get_latest_checkpoint(d.parent, distributed=True) == str(d)
-    total = sum((d / f"shard_{r:05d}.bin").stat().st_size for r in range(world))
+        assert (pyrecover.get_latest_checkpoint(d.parent, distributed=True) == str(d)) == (r == 0)
+    total = sum((d / f"__{r}_0.distcp").stat().st_size for r in range(world))
     assert total >= 3 * opt.arenas[0].layout.payload * 2
+    # stock torch.distributed.checkpoint reads it, with the reference's key names
+    import torch.distributed.checkpoint as dcp
+    prefix = "module." if world > 1 else ""
+    tmpl = {"model": {prefix + k: torch.zeros_like(v, device="cpu") for k, v in model.state_dict().items()},
+            "optimizer": {"state": {i: {"step": torch.zeros(()), "exp_avg": torch.zeros_like(p, device="cpu"),
+                                        "exp_avg_sq": torch.zeros_like(p, device="cpu")}
+                                    for i, p in enumerate(model.parameters())},
+                          "param_groups": [{"lr": 0.0, "betas": (0.0, 0.0), "params": []}]},
+            "metadata": {"epoch": 0, "step": 0}, "lr_scheduler": {"last_epoch": -1}}
+    dcp.load(state_dict=tmpl, checkpoint_id=str(d), no_dist=True)
+    for k, v in model.state_dict().items():
+        assert torch.equal(tmpl["model"][prefix + k], v.cpu()), k
+    for i, p in enumerate(model.parameters()):
+        assert torch.equal(tmpl["optimizer"]["state"][i]["exp_avg"], opt.state[p]["exp_avg"].cpu())
+        assert torch.equal(tmpl["optimizer"]["state"][i]["exp_avg_sq"], opt.state[p]["exp_avg_sq"].cpu())
+        assert float(tmpl["optimizer"]["state"][i]["step"]) == 2.0
+    assert tmpl["metadata"] == {"epoch": 1, "step": 2} and tmpl["lr_scheduler"]["last_epoch"] == sched.last_epoch
+    assert tmpl["optimizer"]["param_groups"][0]["lr"] == opt.param_groups[0]["lr"]
+    assert tmpl["optimizer"]["param_groups"][0]["params"] == list(range(len(list(model.parameters()))))
     m2, o2, s2 = _build(seed=5)
     epoch, step = pyrecover.load_ckpt_distributed(m2, o2, s2, None, "latest", experiment_dir=d.parent)
     assert (epoch, step) == (1, 2) and _equal_models(m2, model)
     assert torch.equal(o2.arenas[0].v, opt.arenas[0].v) and o2._steps[0] == 2
     assert s2.last_epoch == sched.last_epoch
-    f = d / f"shard_{world - 1:05d}.bin"
+    import json
+    f = d / f"__{world - 1}_0.distcp"
     raw = bytearray(f.read_bytes())
-    raw[4096] ^= 1
+    payload = json.loads((d / f"b200_{world - 1:05d}.json").read_text())["pieces"][0][2]
+    raw[payload + 40] ^= 1
     f.write_bytes(bytes(raw))
     with pytest.raises(RuntimeError, match="Checksum mismatch"):
         pyrecover.load_ckpt_distributed(m2, o2, s2, None, str(d))
-    (d / "COMPLETE_00000").unlink()
+    (d / ".metadata").unlink()
     assert pyrecover.get_latest_checkpoint(d.parent, distributed=True) is None
     ck.release_checkpoint_engines()
 
 
 def test_sharded_directory_converts_offline_to_vanilla_and_dcp(cuda_lib, tmp_path):
     """pyrecover.convert reads a sharded directory with nothing but torch on the CPU (the layout table
-    travels in meta.pt): the vanilla file it writes equals save_ckpt_vanilla's tensors, loads back
+    travels in b200_meta.pt): the vanilla file it writes equals save_ckpt_vanilla's tensors, loads back
     through load_ckpt_vanilla, and the DCP directory it writes loads with torch.distributed.checkpoint."""
     import pyrecover
     from pyrecover import checkpoint as ck

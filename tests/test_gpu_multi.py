@@ -51,8 +51,8 @@ def test_two_gpu_train_resume_weight_equality(tmp_path, mode, sharded):
             assert torch.equal(A["optimizer"]["state"][i]["exp_avg_sq"], B["optimizer"]["state"][i]["exp_avg_sq"])
     else:
         for r in range(2):
-            a = (tmp_path / "straight" / "ckpt_20" / f"shard_{r:05d}.bin").read_bytes()
-            b = (tmp_path / "resumed" / "ckpt_20" / f"shard_{r:05d}.bin").read_bytes()
+            a = (tmp_path / "straight" / "ckpt_20" / f"__{r}_0.distcp").read_bytes()
+            b = (tmp_path / "resumed" / "ckpt_20" / f"__{r}_0.distcp").read_bytes()
             assert a == b, f"shard {r} differs"
 
 
@@ -196,7 +196,7 @@ def test_two_gpu_timeaware_stop_rides_in_the_exchange(tmp_path, mode):
     assert len(finals) == 1, out[-3000:]
     step = int(re.search(r"ckpt_(\d+)_final", finals[0].name).group(1))
     assert step > 10 and "[STOP] every rank stops after optimizer step" in out
-    assert (finals[0] / "COMPLETE_00000").exists() and (finals[0] / "COMPLETE_00001").exists()
+    assert (finals[0] / ".metadata").exists() and (finals[0] / "__0_0.distcp").exists() and (finals[0] / "__1_0.distcp").exists()
     r2 = _launch(tmp_path, "ta", step + 5, 2, ("--grad-sync", mode, "--use-torch-distributed-ckpt", "--resume-from-checkpoint",
                                                "latest", "--checkpoint-frequency", "-1"))
     assert f"step {step})" in (r2.stdout + r2.stderr)
