@@ -584,6 +584,11 @@ def run_b200(a):
             tB.append(block(True, i))
             ckpt.wait_for_checkpoints()
             durable.append(time.perf_counter() - t_save0)
+            barrier()
+            if rank == 0:                  # tens of GB per checkpoint at 8 B: never keep two on the disk
+                shutil.rmtree(ckpt_dir / "stall", ignore_errors=True)
+                (ckpt_dir / "stall").mkdir(parents=True, exist_ok=True)
+            barrier()
             tA.append(block(False, 0))
         st = ckpt._snapshotter(trainer.model, opt).last_stats
         barrier()
@@ -654,8 +659,8 @@ def run_b200(a):
             achieved = k2_bytes / (k2_mean * 1e-3) / 1e9 if k2_ms else None
             traffic, traffic_src = None, None
             tf = ROOT / "profiles" / "k2_traffic.json"
-            if tf.exists():
-                tj = json.loads(tf.read_text())
+            tj = json.loads(tf.read_text()) if tf.exists() else {}
+            if tj.get("algorithmic_bytes_per_launch") == int(k2_bytes):      # the capture is of THIS workload's launch
                 traffic = tj.get("dram_bytes_per_launch")
                 traffic_src = ("profiles/k2_traffic.json: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` "
                                "capture of this kernel on this workload (" + str(tj.get("captured", "round 1")) + "); a "

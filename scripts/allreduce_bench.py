@@ -16,6 +16,7 @@ import argparse
 import json
 import os
 import sys
+import time
 from pathlib import Path
 
 import torch
@@ -45,6 +46,49 @@ def timed(fn, iters=20, warmup=5):
     return float(t.item())
 
 
+class NvlinkCounters:
+    """NVLink data-byte counters of one GPU, summed over its links, read through NVML
+    (NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX / _RX, KiB).  A link counter the kernels cannot influence: what
+    `ncu --section NvLink` would show, without putting a profiler around a multi-rank launch."""
+
+    def __init__(self, index: int):
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.read()
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def read(self):
+        nv = self.nv
+        vals = nv.nvmlDeviceGetFieldValues(self.h, [(nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX, 0xFFFFFFFF),
+                                                    (nv.NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_RX, 0xFFFFFFFF)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                raise RuntimeError(f"NVML field {v.fieldId}: return {v.nvmlReturn}")
+            out.append(int(v.value.ullVal) * 1024)
+        return out
+
+
+def link_bytes(counters, fn, launches=10):
+    """(tx, rx) bytes per launch of fn on this rank's GPU."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    time.sleep(0.3)                       # the counters are sampled by the driver, not instantaneous
+    t0, r0 = counters.read()
+    for _ in range(launches):
+        fn()
+    torch.cuda.synchronize()
+    dist.barrier()
+    time.sleep(0.3)
+    t1, r1 = counters.read()
+    return (t1 - t0) / launches, (r1 - r0) / launches
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--min-log2", type=int, default=20)
@@ -53,6 +97,8 @@ def main():
     ap.add_argument("--max-blocks", type=int, default=0)
     ap.add_argument("--fused-max-log2", type=int, default=31, help="largest size for the fused AR+AdamW rows (4 regions)")
     ap.add_argument("--mc-blocks", type=str, default="32,64,148", help="grid sizes tried for the multicast kernels")
+    ap.add_argument("--nvlink-counters", action="store_true", help="NVML link-byte counters around each K1 kernel at 1 GiB")
+    ap.add_argument("--skip-nccl-above-log2", type=int, default=40, help="skip the NCCL rows above this size (time)")
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -219,6 +265,45 @@ def main():
         dist.barrier()
     comm.multicast(-1)
 
+    # ---------------- NVLink byte counters (NVML) around each kernel ---------------------------------
+    if a.nvlink_counters:
+        ctr = NvlinkCounters(local)
+        nb = min(1 << 30, maxb, fmax)
+        ne_ = nb // 2
+        rows = {}
+        if ctr.ok:
+            kernels = {"allreduce_twoshot_kernel (P2P)": (lambda: comm.allreduce(0, 0, nb, torch.bfloat16, scale, algo=_lib.PR_AR_TWO_SHOT),
+                                                          "2 N (W-1)/W per direction", 2 * nb * (world - 1) / world)}
+            if mc_avail:
+                kernels["allreduce_mc_kernel (multicast)"] = (lambda: comm.allreduce(0, 0, nb, torch.bfloat16, scale, algo=_lib.PR_AR_MULTIMEM),
+                                                              "N (1 + 1/W) per direction (reads of the own slice from W-1 peers arrive "
+                                                              "reduced; one multicast store leaves)", nb * (1 + 1 / world))
+                st = [0]
+
+                def fused_mc():
+                    st[0] += 1
+                    comm.allreduce_adamw(0, 1, 2, 3, 0, ne_, K.adamw_args(1e-5, 0.9, 0.999, 1e-8, 0.01, st[0], scale), max_blocks=32)
+                comm.multicast(1)
+                kernels["allreduce_adamw_mc_kernel (fused, multicast)"] = (fused_mc, "N (1 + 1/W) per direction", nb * (1 + 1 / world))
+            nccl_buf = torch.empty(ne_, dtype=torch.bfloat16, device=dev).normal_(0, 1e-3)
+            kernels["ncclAllReduce (reference's DDP)"] = (lambda: dist.all_reduce(nccl_buf), "algorithm-dependent (ring: 2 N (W-1)/W; NVLS: ~N (1+1/W))", None)
+            for name, (fn, formula, predicted) in kernels.items():
+                for _ in range(3):
+                    fn()
+                tx, rx = link_bytes(ctr, fn)
+                rows[name] = {"bytes_allreduced": nb, "tx_bytes_per_launch": tx, "rx_bytes_per_launch": rx, "expected": formula,
+                              "expected_bytes_per_direction": predicted}
+                if rank == 0:
+                    print(f"NVLink counters, {name}: tx {tx / 1e9:.3f} GB rx {rx / 1e9:.3f} GB per launch of {nb / 1e9:.3f} GB "
+                          f"(expected per direction: {predicted / 1e9 if predicted else float('nan'):.3f} GB)", flush=True)
+            comm.multicast(-1)
+            del nccl_buf
+        else:
+            rows = {"unavailable": getattr(ctr, "err", "NVML NVLink counters not readable")}
+            if rank == 0:
+                print("NVLink counters unavailable:", rows["unavailable"], flush=True)
+        results["nvlink_counters_rank0"] = rows
+
     # ---------------- bandwidth sweep -----------------------------------------------------------
     for lg in range(a.min_log2, a.max_log2 + 1):
         nbytes = 1 << lg
@@ -236,7 +321,10 @@ def main():
         if nbytes <= (4 << 20):
             t = timed(lambda: comm.allreduce(0, 0, nbytes, torch.bfloat16, scale, algo=_lib.PR_AR_ONE_SHOT))
             row["oneshot_ms"] = t
-        t = timed(lambda: dist.all_reduce(buf))
+        if lg <= a.skip_nccl_above_log2:
+            t = timed(lambda: dist.all_reduce(buf))
+        else:
+            t = float("nan")
         row["nccl_ms"], row["nccl_busbw"] = t, nbytes / t / 1e6 * 2 * (world - 1) / world
         step = [0]
         if nbytes > fmax:

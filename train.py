@@ -85,6 +85,13 @@ def train(args):
     log_rank0(f"Global batch size: {global_batch_size}\nLocal batch size: {local_batch_size}")
     fetch, vocab_size, train_sampler = build_data(args, local_batch_size, rank)
 
+    if args.deterministic:
+        import os
+        os.environ.setdefault("CUBLAS_WORKSPACE_CONFIG", ":4096:8")
+        torch.use_deterministic_algorithms(True)
+        torch.backends.cudnn.benchmark = False
+        if use_cuda:      # cuDNN's attention backward accumulates with atomics; the flash backend has a deterministic backward
+            torch.backends.cuda.enable_cudnn_sdp(False)
     log_rank0("Setting up Model...")
     torch.manual_seed(args.seed)             # identical initial weights on every rank and every run
     Transformer, model_config = model_args_from_cli(args, vocab_size)

@@ -73,6 +73,10 @@ _ADDITIVE_FLAGS = [
                               help="clip the global gradient norm to --grad-max-norm (the call the reference left "
                                    "commented out at train.py:271-272), folded into the optimizer kernel")),
     ("--sync-checkpoints", dict(action="store_true", help="wait for each checkpoint to be durable before continuing")),
+    ("--deterministic", dict(action="store_true",
+                             help="torch.use_deterministic_algorithms(True): run-to-run identical forward/backward kernels (the "
+                                  "attention backward otherwise accumulates with atomics at larger sizes), so that a straight "
+                                  "run and an interrupted + resumed one can be compared bit for bit at any model size")),
     ("--resubmit-command", dict(type=str, default=None,
                                 help="arm pyrecover.setup_resubmission: on SIGUSR1/SIGTERM write the _final checkpoint and "
                                      "exit; a non-empty value (e.g. 'sbatch submit-training-simple.sh --continue') is run "
