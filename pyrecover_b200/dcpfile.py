@@ -344,12 +344,20 @@ def write_rank_file(path: str, items: List[Item], image_bytes: int, chunks, smal
             for off, blob in it.archive.pieces(c):
                 PT._pwrite_all(fd, memoryview(blob), it.file_off + off)
         cur = end
+        blobs: Dict[Any, Tuple[int, int]] = {}          # identical small items share one blob (147 equal step scalars)
         for key, obj in (small or {}).items():
+            ident = ("t", obj.dtype, tuple(obj.shape), tuple(obj.reshape(-1).tolist())) if torch.is_tensor(obj) and obj.numel() <= 4 \
+                else None
+            if ident is not None and ident in blobs:
+                placed[key] = (name,) + blobs[ident]
+                continue
             buf = io.BytesIO()
             torch.save(obj, buf)
             blob = buf.getvalue()
             PT._pwrite_all(fd, memoryview(blob), cur)
             placed[key] = (name, cur, len(blob))
+            if ident is not None:
+                blobs[ident] = (cur, len(blob))
             cur = _align(cur + len(blob), 8)
         return cur
 
@@ -358,9 +366,11 @@ def write_rank_file(path: str, items: List[Item], image_bytes: int, chunks, smal
 
 
 def write_metadata(dirpath: str, metadata) -> None:
+    """`metadata`: a Metadata object or its pickled bytes (the caller may cache them: nothing in it changes from
+    save to save as long as the small items keep their sizes)."""
     tmp = os.path.join(dirpath, ".metadata.tmp")
     with open(tmp, "wb") as f:
-        pickle.dump(metadata, f)
+        f.write(metadata if isinstance(metadata, (bytes, bytearray)) else pickle.dumps(metadata))
         f.flush()
         os.fsync(f.fileno())
     os.replace(tmp, os.path.join(dirpath, ".metadata"))
