@@ -70,7 +70,10 @@ def _read_sharded(d: Path) -> Dict[str, Any]:
         nbytes = numel * torch.empty((), dtype=dt).element_size()
         return buf[off:off + nbytes].view(dt).reshape(shape).clone()
 
-    model = OrderedDict((k, view(e)) for k, e in layout["model"].items() if e is not None)
+    missing = [k for k, e in layout["model"].items() if e is None]
+    if missing:          # written by an older build that allowed state outside the image: nothing here could restore it
+        raise RuntimeError(f"{d}: model entries without a place in the checkpoint image: {missing[:5]}")
+    model = OrderedDict((k, view(e)) for k, e in layout["model"].items())
     steps = meta.get("opt_steps", [0])
     opt_state = {}
     for i, ent in layout["optimizer"].items():
