@@ -135,7 +135,7 @@ def run_reference(a):
         return 0
     from oracle import cpu_reference_port as port
     world = max(1, a.gpus)
-    steps, warmup = max(1, a.steps), max(1, min(a.warmup, 2))
+    steps, warmup = max(1, a.steps), (1 if world > 1 else max(1, min(a.warmup, 2)))
     tmp = a.ckpt_dir or tempfile.mkdtemp(prefix="pr_ref_")
     unavailable = None
     if world > 1:
@@ -156,8 +156,8 @@ def run_reference(a):
             res = port.run(a.preset, a.seq, steps=steps, warmup=warmup, fused=True, budget_s_per_step=a.cpu_budget_s,
                            ckpt_path=os.path.join(tmp, "ckpt_ref.pt"))
         else:
-            res = port.run_ddp(a.preset, a.seq, steps=steps, warmup=warmup, world=world, fused=True,
-                               budget_s_per_step=a.cpu_budget_s)
+            res = port.run_ddp(a.preset, a.seq, steps=min(steps, 8), warmup=1, world=world, fused=True,
+                               budget_s_per_step=a.cpu_budget_s)      # every step carries a gloo all-reduce of the model: keep it to minutes
     except Exception as e:  # noqa: BLE001 -- the arm reports, it never takes the driver's run down
         print(json.dumps({"impl": "reference", "metric": METRIC, "value": None, "unit": "tokens/s", "n_gpus": a.gpus,
                           "unavailable": f"{type(e).__name__}: {e}", "config": _config(a.preset, None, world, a.seq)}), flush=True)
