@@ -36,6 +36,14 @@ import zlib
 from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import torch
+# Imported HERE, at start-up, and not inside the functions that need them: the first import of
+# torch.distributed.checkpoint takes seconds (4.7 s from a cold page cache), and those functions run in rank 0's
+# writer thread beside the training loop -- an import there holds the interpreter lock against the training thread of
+# ONE rank for that long, and every other rank waits for it in the gradient exchange.
+from torch.distributed.checkpoint._nested_dict import flatten_state_dict
+from torch.distributed.checkpoint.filesystem import _StorageInfo
+from torch.distributed.checkpoint.metadata import (BytesStorageMetadata, ChunkStorageMetadata, Metadata, MetadataIndex,
+                                                   StorageMeta, TensorProperties, TensorStorageMetadata)
 
 from . import ptfile as PT
 
@@ -205,7 +213,6 @@ def small_state_items(small_state: Dict[str, Any], n_params: int) -> Tuple[Dict[
     items: ({flat key: object or small tensor}, {flat key: path}).  `small_state` carries epoch, step,
     param_groups (with "params" index lists), opt_steps, lr_scheduler, sampler_state -- what
     pyrecover/checkpoint.py:254-264 hands to dist_cp.save besides the tensors."""
-    from torch.distributed.checkpoint._nested_dict import flatten_state_dict
     groups = small_state["param_groups"]
     steps = small_state.get("opt_steps", [0] * len(groups))
     opt_state = {}
@@ -239,9 +246,6 @@ def build_metadata(table, plans: Dict[int, List[Item]], small_flat: Dict[str, An
                    small_storage: Dict[str, Tuple[str, int, int]]):
     """torch.distributed.checkpoint's Metadata for the directory: every tensor with the boxes all ranks
     wrote, every small item, and where each lives (file, offset, length)."""
-    from torch.distributed.checkpoint.filesystem import _StorageInfo
-    from torch.distributed.checkpoint.metadata import (BytesStorageMetadata, ChunkStorageMetadata, Metadata, MetadataIndex,
-                                                       StorageMeta, TensorProperties, TensorStorageMetadata)
     sdm: Dict[str, Any] = {}
     storage: Dict[Any, Any] = {}
     boxes: Dict[str, List[Tuple[Item, int]]] = {}

@@ -301,6 +301,9 @@ class Snapshotter:
                 pieces.append(Piece(flat[lo:lo + it.nbytes], it.payload_off, global_off=it.global_off))
             self._shard = Image(pieces, nbytes, self.device, self.mode == "staged")
             self._shard_key = (rank, world)
+            if rank == 0:                          # rank 0 lays out every rank's file for .metadata: do it now, not in the
+                for r in range(world):             # writer thread beside the training loop
+                    self.dcp_plan(r, world)
         return self._shard
 
     def _locate(self, t: torch.Tensor) -> Optional[Tuple[str, int]]:
