@@ -29,7 +29,6 @@ DistributedDataParallel wrapper, i.e. world > 1), "optimizer.state.<i>.{step,exp
 from __future__ import annotations
 
 import io
-import json
 import os
 import pickle
 import zlib

@@ -40,7 +40,6 @@ from typing import List, Optional
 import torch
 from torch.cuda import nvtx
 
-from . import _lib
 from . import kernels as K
 from .flat import FlatArena
 

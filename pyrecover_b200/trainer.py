@@ -8,7 +8,7 @@ gloo + torch.optim.AdamW -- because that IS the reference path there, not a fall
 """
 from __future__ import annotations
 
-from typing import Optional, Tuple
+from typing import Optional
 
 import torch
 import torch.nn.functional as F

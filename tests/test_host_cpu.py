@@ -696,3 +696,49 @@ def test_policy_learns_from_durable_checkpoint_time_and_signal_stops(tmp_path):
         assert st.stop_requested and st.resubmitted and marker.exists()
     finally:
         signal.signal(signal.SIGUSR1, old)
+
+
+def test_flat_ranges_become_contiguous_boxes():
+    """dcpfile.flat_range_boxes: any flat element range of a row-major tensor is covered exactly once, in order,
+    by at most 2 * ndim - 1 boxes, each contiguous in memory (what lets a reduce-scatter slice be written as
+    torch.distributed.checkpoint chunks without moving a byte)."""
+    import random
+
+    from pyrecover_b200.dcpfile import flat_range_boxes
+    rng = random.Random(7)
+    for shape in [(7,), (5, 6), (3, 4, 5), (2, 3, 4, 5), (1, 9), (6, 1), ()]:
+        n = int(np.prod(shape)) if shape else 1
+        t = torch.arange(n).reshape(shape)
+        for _ in range(150):
+            lo = rng.randrange(0, n)
+            hi = rng.randrange(lo, n + 1)
+            boxes = flat_range_boxes(shape, lo, hi)
+            assert len(boxes) <= max(1, 2 * len(shape) - 1)
+            got = []
+            for off, sz, first in boxes:
+                sub = t[tuple(slice(o, o + s) for o, s in zip(off, sz))] if shape else t
+                flat = sub.reshape(-1)
+                assert torch.equal(flat, torch.arange(first, first + flat.numel()))      # contiguous run of the flat order
+                got.append(flat)
+            got = torch.cat(got) if got else torch.empty(0, dtype=torch.long)
+            if shape:
+                assert torch.equal(got, torch.arange(lo, hi))
+    assert flat_range_boxes((4, 4), 5, 5) == []
+
+
+def test_pack_grid_follows_image_size_and_step_period():
+    """snapshot.pack_blocks_for: the pack that runs beside the next forward is spread over ~0.7 of a step
+    (one CTA moves ~85 GB/s): 8 CTAs for the 6 GB image of the 1 B model at a 25 ms step, the 4-CTA floor for a
+    0.75 GB shard, all SMs at most; an explicit PYRECOVER_B200_PACK_BLOCKS wins."""
+    from pyrecover_b200 import snapshot as S
+    assert S.pack_blocks_for(6_040_203_264, 0.0254) == 8
+    assert S.pack_blocks_for(755_000_000, 0.028) == 4
+    assert S.pack_blocks_for(48_000_000_000, 0.15) == 11
+    assert S.pack_blocks_for(48_000_000_000, 0.001) == 148
+    assert S.pack_blocks_for(6_040_203_264, None) == 10
+    old = S.PACK_BLOCKS
+    try:
+        S.PACK_BLOCKS = 32
+        assert S.pack_blocks_for(6_040_203_264, 0.0254) == 32
+    finally:
+        S.PACK_BLOCKS = old
